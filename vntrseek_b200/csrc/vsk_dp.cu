@@ -1,0 +1,320 @@
+// Profile-to-profile global alignment kernels (the PROCLU DP).
+//
+// Replaces GetFixedProfileAP (reference src/psearch1.91/profile.h:2040-2227) and
+// GetFixedProfileAPNarrowband (profile.h:1733-2038).  One pair per warp.  The
+// (L1+1)x(L2+1) matrix is swept in strips of 32*CPL columns; inside a strip
+// lane k owns CPL consecutive columns and trails lane k-1 by one row, so the 32
+// lanes sit on an anti-diagonal wavefront and the cell to the left of a lane's
+// strip arrives by __shfl_up_sync.  The previous row of a lane's columns lives
+// in registers.  The reference stores a direction per cell and walks back from
+// the corner summing dashnum*cost and dashnum (profile.h:2180-2210); here each
+// cell carries those two sums (and the path length) of its chosen predecessor
+// forward, so nothing but the running wavefront is ever stored.
+//
+// Substitution costs: the reference gathers from the 501,501-byte triangular
+// table per cell.  Per pair the warp builds the two local alphabets (distinct
+// composition ids of each profile) and a compact na x nb byte table in shared
+// memory; the per-cell gather is then a conflict-light LDS.  Pairs whose compact
+// table would not fit fall back to gathering from the full symmetric table in
+// global memory (L1/L2 resident).
+//
+// Narrowband: the band of the reference (per-row lstart/rend from IEEE double
+// row*svector, profile.h:1835-1839) is applied as a mask: out-of-band cells are
+// VSK_BIG, exactly the value of the sentinels the reference plants beside the
+// band (profile.h:1850-1877), so they never win or tie against in-band cells.
+#include "vsk_internal.cuh"
+
+#define DP_WARPS 4
+#define DP_TBYTES 8192
+#define FULLMASK 0xffffffffu
+
+struct DpWarpSmem {
+    uint8_t T[DP_TBYTES];   // compact substitution table [na][nb]
+    uint8_t mapL[1024];     // global id -> local row index
+    uint32_t bmL[32];       // presence bitmaps over ids 0..1023
+    uint32_t bmT[32];
+    uint16_t preT[32];      // exclusive popcount prefix of bmT
+    uint16_t invL[256];     // local -> global id
+    uint16_t invT[256];
+};
+
+#define DP_SMEM_BYTES (2048 + DP_WARPS * sizeof(DpWarpSmem))
+
+template <int CPL, bool MASKED, bool SMEMT>
+__device__ __forceinline__ void dp_row_cells(int (&Hd)[CPL], int (&Hp1)[CPL], int (&Hp2)[CPL],
+                                             const int (&tb)[CPL], const int (&gt)[CPL],
+                                             const int (&ci1)[CPL], const int (&ci2)[CPL], int dgd,
+                                             int dgp1, int dgp2, int lfd, int lfp1, int lfp2,
+                                             const uint8_t *__restrict__ trow, int gl, int ndl,
+                                             int ri1, int ri2, int lo, int hi) {
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+        const int upd = Hd[j], upp1 = Hp1[j], upp2 = Hp2[j];
+        const int dlt = SMEMT ? (int)trow[tb[j]] : (int)__ldg(trow + tb[j]);
+        const int sa = dgd + dlt;  // diagonal
+        const int f = upd + gl;    // down  (gap in the read / top profile)
+        const int e = lfd + gt[j]; // right (gap in the reference / left profile)
+        // min3switch (profile.h:1098-1099): diag if sa<=f && sa<=e; else down if f<=e; else right
+        const bool pF = f <= e;
+        const int m1 = pF ? f : e;
+        const bool pD = sa <= m1;
+        int d = pD ? sa : m1;
+        int dn = ndl + ci2[j] - VSK_LEN1;  // NONDASHES[l] + NONDASHES[t]
+        dn = dn < 10 ? dn : 10;
+        const int p1d = dgp1 + dn * dlt, p2d = dgp2 + dn + VSK_LEN1;
+        const int p1f = upp1 + ri1, p2f = upp2 + ri2;
+        const int p1e = lfp1 + ci1[j], p2e = lfp2 + ci2[j];
+        const int p1 = pD ? p1d : (pF ? p1f : p1e);
+        const int p2 = pD ? p2d : (pF ? p2f : p2e);
+        if (MASKED) {
+            if (j < lo || j > hi) d = VSK_BIG;
+        }
+        dgd = upd; dgp1 = upp1; dgp2 = upp2;
+        Hd[j] = d; Hp1[j] = p1; Hp2[j] = p2;
+        lfd = d; lfp1 = p1; lfp2 = p2;
+    }
+}
+
+template <int CPL, bool SMEMT>
+__device__ __forceinline__ void dp_pair(const vsk_dp_job &job, const uint16_t *__restrict__ L,
+                                     const uint16_t *__restrict__ Tp,
+                                     const uint8_t *__restrict__ dist, const uint16_t *s_gapnd,
+                                     DpWarpSmem &ws, int nb, int4 *scratch, int4 *out) {
+    const int lane = threadIdx.x & 31;
+    const int l1 = job.l1, l2 = job.l2, br = job.br;
+    const bool banded = br >= 0;
+    const double sv = job.svector;
+    const int npass = (l2 + 32 * CPL - 1) / (32 * CPL);
+    int totd = 0, totp1 = 0, totp2 = 0;  // row-0 prefix over the strips already done
+    int Hd[CPL], Hp1[CPL], Hp2[CPL];
+
+    for (int pass = 0; pass < npass; ++pass) {
+        const int cbase = pass * 32 * CPL + lane * CPL;  // matrix column left of this lane's strip
+        int tb[CPL], gt[CPL], ci1[CPL], ci2[CPL];
+        int sd = 0, s1 = 0, s2 = 0;
+#pragma unroll
+        for (int j = 0; j < CPL; ++j) {
+            const int c = cbase + j;
+            const int id = (c < l2) ? (int)Tp[c] : 0;  // id 0: gap cost 0, no non-dash symbols
+            const int gn = s_gapnd[id];
+            const int g = gn & 255, nd = gn >> 8;
+            gt[j] = g;
+            ci1[j] = nd * g;
+            ci2[j] = nd + VSK_LEN1;
+            if (SMEMT) {
+                const int w = id >> 5;
+                tb[j] = ws.preT[w] + __popc(ws.bmT[w] & ((1u << (id & 31)) - 1u));
+            } else {
+                tb[j] = id;
+            }
+            sd += g; s1 += nd * g; s2 += nd + VSK_LEN1;
+            Hd[j] = sd; Hp1[j] = s1; Hp2[j] = s2;
+        }
+        // row 0 (profile.h:2074-2079): cumulative gap costs; exclusive warp scan
+        int xd = sd, x1 = s1, x2 = s2;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int a = __shfl_up_sync(FULLMASK, xd, o);
+            const int b = __shfl_up_sync(FULLMASK, x1, o);
+            const int c = __shfl_up_sync(FULLMASK, x2, o);
+            if (lane >= o) { xd += a; x1 += b; x2 += c; }
+        }
+        const int ed = xd - sd + totd, e1 = x1 - s1 + totp1, e2 = x2 - s2 + totp2;
+#pragma unroll
+        for (int j = 0; j < CPL; ++j) {
+            Hd[j] += ed; Hp1[j] += e1; Hp2[j] += e2;
+            if (banded && cbase + j + 1 > br) Hd[j] = VSK_BIG;  // profile.h:1801-1802
+        }
+        int dgd = ed, dgp1 = e1, dgp2 = e2;  // (row 0, column cbase)
+        if (banded && cbase > br) dgd = VSK_BIG;
+        totd += __shfl_sync(FULLMASK, xd, 31);
+        totp1 += __shfl_sync(FULLMASK, x1, 31);
+        totp2 += __shfl_sync(FULLMASK, x2, 31);
+
+        const bool rd_scratch = (lane == 0) && (pass > 0);
+        const bool wr_scratch = (lane == 31) && (pass < npass - 1);
+        int4 nxt = make_int4(0, 0, 0, 0);
+        if (rd_scratch) nxt = __ldcg(scratch);
+
+        const int nsteps = l1 + 31;
+        for (int s = 0; s < nsteps; ++s) {
+            const int r = s - lane;  // 0-based row of the reference (left) profile
+            int lfd = __shfl_up_sync(FULLMASK, Hd[CPL - 1], 1);
+            int lfp1 = __shfl_up_sync(FULLMASK, Hp1[CPL - 1], 1);
+            int lfp2 = __shfl_up_sync(FULLMASK, Hp2[CPL - 1], 1);
+            const bool active = (r >= 0) && (r < l1);
+            int gl = 0, ndl = 0, ri1 = 0, ri2 = 0, lo = 0, hi = CPL;
+            const uint8_t *trow = SMEMT ? ws.T : dist;
+            bool need_mask = false;
+            if (active) {
+                const int id = L[r];
+                const int gn = s_gapnd[id];
+                gl = gn & 255;
+                ndl = gn >> 8;
+                ri1 = ndl * gl;
+                ri2 = ndl + VSK_LEN1;
+                trow += SMEMT ? (int)ws.mapL[id] * nb : id * VSK_DROW;
+                if (lane == 0) {
+                    if (pass == 0) {  // column 0 (profile.h:2084-2090): cumulative gap costs
+                        lfd = dgd + gl; lfp1 = dgp1 + ri1; lfp2 = dgp2 + ri2;
+                    } else {
+                        lfd = nxt.x; lfp1 = nxt.y; lfp2 = nxt.z;
+                        if (r + 1 < l1) nxt = __ldcg(scratch + r + 1);
+                    }
+                }
+                if (banded) {  // profile.h:1835-1839
+                    const int center = __double2int_rz(__dmul_rn((double)(r + 1), sv));
+                    const int lstart = max(1, center - br);
+                    const int rend = min(l2, center + br);
+                    lo = lstart - (cbase + 1);
+                    hi = rend - (cbase + 1);
+                    need_mask = (lo > 0) || (hi < CPL - 1);
+                }
+            }
+            const bool anymask = banded && __any_sync(FULLMASK, need_mask);
+            if (active) {
+                if (anymask)
+                    dp_row_cells<CPL, true, SMEMT>(Hd, Hp1, Hp2, tb, gt, ci1, ci2, dgd, dgp1, dgp2,
+                                                   lfd, lfp1, lfp2, trow, gl, ndl, ri1, ri2, lo, hi);
+                else
+                    dp_row_cells<CPL, false, SMEMT>(Hd, Hp1, Hp2, tb, gt, ci1, ci2, dgd, dgp1, dgp2,
+                                                    lfd, lfp1, lfp2, trow, gl, ndl, ri1, ri2, lo, hi);
+                dgd = lfd; dgp1 = lfp1; dgp2 = lfp2;
+                if (wr_scratch) scratch[r] = make_int4(Hd[CPL - 1], Hp1[CPL - 1], Hp2[CPL - 1], 0);
+            }
+        }
+        __syncwarp();  // scratch written by lane 31 is read by lane 0 in the next strip
+    }
+    const int cl = (l2 - 1) - (npass - 1) * 32 * CPL;
+    if (lane == cl / CPL) {
+        const int jr = cl % CPL;
+#pragma unroll
+        for (int j = 0; j < CPL; ++j)
+            if (j == jr)
+                out[job.out_idx] = make_int4(Hd[j], Hp1[j], Hp2[j] & (VSK_LEN1 - 1), Hp2[j] >> 17);
+    }
+}
+
+__global__ void __launch_bounds__(DP_WARPS * 32)
+vsk_dp_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
+              const vsk_dp_job *__restrict__ jobs, int n_jobs, const uint8_t *__restrict__ dist,
+              const uint16_t *__restrict__ gapnd, int4 *scratch, int scratch_stride, int *queue,
+              int4 *out) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(smem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    DpWarpSmem &ws = reinterpret_cast<DpWarpSmem *>(smem + 2048)[warp];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_gapnd[i] = gapnd[i];
+    __syncthreads();
+    int4 *my_scratch = scratch + (size_t)(blockIdx.x * DP_WARPS + warp) * scratch_stride;
+
+    for (;;) {
+        int ji = 0;
+        if (lane == 0) ji = atomicAdd(queue, 1);
+        ji = __shfl_sync(FULLMASK, ji, 0);
+        if (ji >= n_jobs) break;
+        const vsk_dp_job job = jobs[ji];
+        const uint16_t *L = left_ids + job.left_off;
+        const uint16_t *Tp = top_ids + job.top_off;
+        const int l1 = job.l1, l2 = job.l2;
+
+        // local alphabets
+        ws.bmL[lane] = 0;
+        ws.bmT[lane] = 0;
+        __syncwarp();
+        for (int i = lane; i < l1; i += 32) {
+            const int id = L[i];
+            atomicOr(&ws.bmL[id >> 5], 1u << (id & 31));
+        }
+        for (int i = lane; i < l2; i += 32) {
+            const int id = Tp[i];
+            atomicOr(&ws.bmT[id >> 5], 1u << (id & 31));
+        }
+        __syncwarp();
+        const uint32_t bl = ws.bmL[lane], bt = ws.bmT[lane];
+        int xl = __popc(bl), xt = __popc(bt);
+        const int cl = xl, ct = xt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int a = __shfl_up_sync(FULLMASK, xl, o);
+            const int b = __shfl_up_sync(FULLMASK, xt, o);
+            if (lane >= o) { xl += a; xt += b; }
+        }
+        const int na = __shfl_sync(FULLMASK, xl, 31), nb = __shfl_sync(FULLMASK, xt, 31);
+        const bool smemt = (na <= 256) && (nb <= 256) && (na * nb <= DP_TBYTES);
+        if (smemt) {
+            ws.preT[lane] = (uint16_t)(xt - ct);
+            uint32_t b = bl;
+            int rk = xl - cl;
+            while (b) {
+                const int id = lane * 32 + __ffs(b) - 1;
+                b &= b - 1;
+                ws.mapL[id] = (uint8_t)rk;
+                ws.invL[rk] = (uint16_t)id;
+                ++rk;
+            }
+            b = bt;
+            rk = xt - ct;
+            while (b) {
+                const int id = lane * 32 + __ffs(b) - 1;
+                b &= b - 1;
+                ws.invT[rk] = (uint16_t)id;
+                ++rk;
+            }
+            __syncwarp();
+#pragma unroll 4
+            for (int a = 0; a < na; ++a) {
+                const uint8_t *drow = dist + (int)ws.invL[a] * VSK_DROW;
+                for (int c = lane; c < nb; c += 32) ws.T[a * nb + c] = __ldg(drow + ws.invT[c]);
+            }
+            __syncwarp();
+        }
+#define DP_DISPATCH(CPLV)                                                                         \
+    do {                                                                                          \
+        if (smemt) dp_pair<CPLV, true>(job, L, Tp, dist, s_gapnd, ws, nb, my_scratch, out);       \
+        else dp_pair<CPLV, false>(job, L, Tp, dist, s_gapnd, ws, nb, my_scratch, out);            \
+    } while (0)
+        if (l2 <= 32) DP_DISPATCH(1);
+        else if (l2 <= 64) DP_DISPATCH(2);
+        else if (l2 <= 128) DP_DISPATCH(4);
+        else DP_DISPATCH(8);
+#undef DP_DISPATCH
+        __syncwarp();
+    }
+}
+
+static int g_dp_attr_set = 0;
+
+int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids,
+                  const vsk_dp_job *d_jobs, int64_t n_jobs, int32_t max_l1, int4 *d_out) {
+    if (n_jobs <= 0) return VSK_OK;
+    if (n_jobs > 0x7fffffff) return vsk_fail(ctx, VSK_ERR_ARG, "too many DP pairs in one launch");
+    if (!g_dp_attr_set) {
+        VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)DP_SMEM_BYTES));
+        g_dp_attr_set = 1;
+    }
+    int per_sm = 0;
+    VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_kernel, DP_WARPS * 32,
+                                                                 DP_SMEM_BYTES));
+    if (per_sm < 1) per_sm = 1;
+    int64_t grid = (int64_t)ctx->sm_count * per_sm;  // persistent: one wave, work pulled from a queue
+    const int64_t need = (n_jobs + DP_WARPS - 1) / DP_WARPS;
+    if (grid > need) grid = need;
+    const int stride = ((max_l1 + 31) / 32) * 32;
+    const size_t bytes = (size_t)grid * DP_WARPS * stride * sizeof(int4);
+    if (bytes > ctx->dp_scratch_bytes) {
+        if (ctx->d_dp_scratch) VSK_CUDA(ctx, cudaFree(ctx->d_dp_scratch));
+        ctx->d_dp_scratch = nullptr;
+        ctx->dp_scratch_bytes = 0;
+        VSK_CUDA(ctx, cudaMalloc(&ctx->d_dp_scratch, bytes));
+        ctx->dp_scratch_bytes = bytes;
+    }
+    VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
+    vsk_dp_kernel<<<(unsigned)grid, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
+        d_left_ids, d_top_ids, d_jobs, (int)n_jobs, ctx->d_dist, ctx->d_gapnd,
+        (int4 *)ctx->d_dp_scratch, stride, ctx->d_queue, d_out);
+    ctx->launches++;
+    VSK_CUDA(ctx, cudaGetLastError());
+    return VSK_OK;
+}

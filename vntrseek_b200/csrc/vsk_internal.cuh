@@ -1,0 +1,75 @@
+// Internal declarations shared by the libvsk translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/vsk.h"
+
+#define VSK_NIDS 1001
+#define VSK_DROW 1024        // padded row stride of the symmetric distance table
+#define VSK_BIG 100000000    // out-of-band sentinel (reference: profile.h:1802)
+#define VSK_LEN1 (1 << 17)   // path-length unit packed above sumw (sumw <= 10*(L1+L2) < 2^17)
+#define VSK_MAXPROF 6000     // longest profile accepted by the DP kernels
+
+struct vsk_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    uint8_t *d_dist = nullptr;    // [VSK_NIDS][VSK_DROW] symmetric distances
+    uint16_t *d_gapnd = nullptr;  // [1024]: d(0,id) | NONDASHES[id] << 8
+    uint8_t h_nd[VSK_NIDS];
+    uint8_t h_gap[VSK_NIDS];
+    // DP scratch (boundary columns between column strips), grown on demand
+    void *d_dp_scratch = nullptr;
+    size_t dp_scratch_bytes = 0;
+    int *d_queue = nullptr;       // dynamic work counter
+    std::string err;
+    uint64_t launches = 0;        // kernels launched through this context
+};
+
+struct vsk_profset {
+    int32_t n = 0;
+    int64_t total = 0;
+    int64_t *d_off = nullptr;   // [n+1]
+    uint16_t *d_ids = nullptr;  // [total]
+    std::vector<int64_t> h_off; // host copy of the offsets (lengths are needed for scheduling)
+};
+
+int vsk_fail(vsk_ctx *ctx, int code, const char *fmt, ...);
+
+#define VSK_CUDA(ctx, call)                                                              \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess)                                                          \
+            return vsk_fail((ctx), VSK_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, \
+                            cudaGetErrorString(e__));                                    \
+    } while (0)
+
+// Band geometry of the narrowband aligner computed with the host libm in the
+// same operation order as the reference (profile.h:1752-1770).
+void vsk_band_host(int leftlen, int toplen, int homology, double *svector, int *br);
+
+// kernels / launchers -----------------------------------------------------
+struct vsk_dp_job {   // one pair as the kernel sees it (sorted by cost, heaviest first)
+    int64_t left_off, top_off;
+    int32_t l1, l2;
+    int32_t br;       // band radius, <0 = full matrix
+    int32_t out_idx;  // where the result goes
+    double svector;
+};
+
+int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids,
+                  const vsk_dp_job *d_jobs, int64_t n_jobs, int32_t max_l1, int4 *d_out);
+
+int vsk_lcs_launch(vsk_ctx *ctx, const uint8_t *d_seqA, const int64_t *d_offA, const uint8_t *d_seqB,
+                   const int64_t *d_offB, const int32_t *d_ia, const int32_t *d_ib, int64_t n,
+                   int32_t *d_out);
+
+int vsk_ed_launch(vsk_ctx *ctx, const uint8_t *d_text, const int64_t *d_toff, const int32_t *d_tlen,
+                  const uint8_t *d_pat, const int64_t *d_poff, const int32_t *d_plen, int64_t n,
+                  int variant, int32_t *d_out);
