@@ -106,6 +106,91 @@ int vsk_ed_pairs(vsk_ctx *ctx, const char *text, const int64_t *t_off, const int
                  const char *pat, const int64_t *p_off, const int32_t *p_len, int64_t n,
                  int variant, int32_t *out);
 
+
+/* ---- TR sets (.leb36 files in memory) ----------------------------------------
+ * ReadProfileWithRC (profile.h:448-732): record i owns profile 2i (as written)
+ * and 2i+1 (its reverse complement, as written), the consensus of each without
+ * dash columns, and the flanks (left reversed; rc = complemented and swapped;
+ * upper-cased, non-ACGT -> N; read flanks cut to maxflank, -r mode to reflen). */
+typedef struct vsk_trset vsk_trset;
+int vsk_trset_load_leb36(const char *path, int is_read, int maxflank, int option_r, int reflen,
+                         vsk_trset **out);
+/* same from arrays: prof_off[2n+1] into ids; flank_off[2n+1] into flanks (left,
+ * right per record, as they stand in the file: left NOT reversed)             */
+int vsk_trset_from_arrays(int32_t n, const int32_t *key, const int32_t *patlen,
+                          const int64_t *prof_off, const uint16_t *ids, const int64_t *flank_off,
+                          const char *flanks, int is_read, int maxflank, int option_r, int reflen,
+                          vsk_trset **out);
+/* LoadRotated (psearch.c:1086-1201); a missing file is fine (returns VSK_OK). */
+int vsk_trset_apply_rotindex(vsk_trset *ts, const char *path);
+/* psearch.c:397-401,424-428: a key may appear once across both files */
+int vsk_trsets_check_unique(const vsk_trset *a, const vsk_trset *b, int32_t *dup_key);
+int32_t vsk_trset_size(const vsk_trset *ts);
+const char *vsk_trset_error(const vsk_trset *ts);
+void vsk_trset_free(vsk_trset *ts);
+
+/* ---- PROCLU ---------------------------------------------------------------------
+ * vsk_refs_create = everything doSearchSimilarities does to the reference set
+ * before the scan (psearch.c:507-766): seed every master profile into its TRANGE
+ * (and neighbours), order the buckets as the reference's sort leaves them, and
+ * place TR set + index in HBM.  The TR set must outlive the handle.            */
+typedef struct vsk_refs vsk_refs;
+typedef struct vsk_reads vsk_reads;
+typedef struct vsk_proclu_result vsk_proclu_result;
+int vsk_refs_create(vsk_ctx *ctx, const vsk_trset *refs, vsk_refs **out);
+void vsk_refs_free(vsk_ctx *ctx, vsk_refs *refs);
+int64_t vsk_refs_seed_hits(const vsk_refs *refs);
+
+typedef struct {
+    int32_t cutoff;      /* argv CUTOFF 70..100 (psearch.c:909-912)                  */
+    int32_t maxerrors;   /* argv MAXERRORS, 0 = from flank length (hclust.h:660-668)  */
+    int32_t option_r;    /* -r: not yet on the GPU path (rejected)                   */
+    int32_t reserved;
+    int64_t key_budget;  /* candidate keys per chunk, 0 = default                    */
+} vsk_proclu_params;
+
+typedef struct {                          /* BLASTSTATS, hclust.h:43-51 */
+    uint64_t candidates_considered;       /* stCandidatesConsidered                  */
+    uint64_t lcs_alignments;              /* stLCSalignments                         */
+    uint64_t profile_alignments;          /* stProfileAlignments                     */
+    uint64_t profile_alignments_success;  /* stProfileAlignmentsSuccess              */
+    uint64_t confirmed;                   /* stPairsConfirmedAfterFlankAlignments    */
+    int64_t dp_cells;                     /* DP cells the reference would evaluate   */
+    int64_t candidate_keys;               /* keys materialised before dedup          */
+    int64_t chunks;
+    int64_t h2d_bytes, d2h_bytes;
+} vsk_proclu_stats;
+
+typedef struct {       /* one ClusterBaseAddLink call (hclust.h:813-822), in call order */
+    int32_t refkey, readkey;
+    int32_t dir, lerr, rerr;
+    int32_t dsum, sumw;  /* bestsim = 1.0 - dsum/(255.0*sumw) */
+} vsk_link;
+
+/* The per-read scan (psearch.c:777-845) for a whole read file: host buffers in,
+ * links out (H2D of the reads and D2H of the links inside the call).           */
+int vsk_proclu_run(vsk_ctx *ctx, const vsk_refs *refs, const vsk_trset *reads,
+                   const vsk_proclu_params *prm, vsk_proclu_result **out);
+/* same with the read set already resident in HBM */
+int vsk_reads_upload(vsk_ctx *ctx, const vsk_trset *reads, vsk_reads **out);
+void vsk_reads_free(vsk_ctx *ctx, vsk_reads *reads);
+int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *refs, const vsk_reads *reads,
+                            const vsk_proclu_params *prm, vsk_proclu_result **out);
+int64_t vsk_proclu_result_links(const vsk_proclu_result *r, const vsk_link **links);
+void vsk_proclu_result_stats(const vsk_proclu_result *r, vsk_proclu_stats *stats);
+void vsk_proclu_result_free(vsk_proclu_result *r);
+
+/* ClusterBaseAddLink over the links in order + ClusterBasePrint (cluster.h:268-332,
+ * 452-541) -> `<reads>.clu`; map_path != NULL also writes the -m map lines
+ * (hclust.h:818-822).  *trcount = CLUSTERBASE.trcount ("total clustered").      */
+int vsk_clusters_write(const vsk_link *links, int64_t n, const char *clu_path, const char *map_path,
+                       uint64_t *trcount);
+
+/* Edges mode (doEdgesBruteForce, psearch.c:1223-1405): `id1,id2` lines in, one
+ * `id1{'|"},id2,%.4lf` line per edge + `#ave:` out.                              */
+int vsk_edges_run(vsk_ctx *ctx, const vsk_trset *a, const vsk_trset *b, const char *edgein_path,
+                  const char *out_path, int64_t *n_edges);
+
 #ifdef __cplusplus
 }
 #endif

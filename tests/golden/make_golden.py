@@ -145,3 +145,23 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def psearch_small():
+    """tests/golden/psearch_small: a small synthetic .leb36 pair (+.rotindex) and what the
+    reference psearch.exe (oracle/_ref, unmodified sources) made of it: .clu + stderr log."""
+    import subprocess
+    d = os.path.join(HERE, "psearch_small")
+    os.makedirs(d, exist_ok=True)
+    refs = synth.make_refs(250, seed=11, max_patlen=300, rot_frac=0.04)
+    reads = synth.make_reads(refs, 300, seed=12, rot_frac=0.03)
+    refs.write_leb36(os.path.join(d, "reference.leb36"))
+    reads.write_leb36(os.path.join(d, "reads.leb36"))
+    p = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "psearch.exe"), "reference.leb36", "reads.leb36",
+                        os.path.join(ROOT, "oracle", "_ref", "eucledian.dst"), "88", "0", "50"],
+                       cwd=d, capture_output=True, text=True, check=True)
+    open(os.path.join(d, "ref.log"), "w").write(p.stderr)
+
+
+if __name__ == "__main__":
+    psearch_small()

@@ -1,0 +1,82 @@
+"""GPU, file level: the drop-in psearch.exe against the reference psearch.exe
+(oracle/_ref, compiled from the unmodified reference sources) on the same
+.leb36 / .rotindex files: the six stderr counters, the canonical .clu, and -- in
+edges mode -- the byte-exact .edges file."""
+import filecmp
+import os
+import shutil
+
+import numpy as np
+import pytest
+
+from _cli import OUR_BIN, REF_BIN, canonical_clu, parse_counters, run
+
+pytestmark = pytest.mark.gpu
+
+
+def _have_ref():
+    return os.path.exists(os.path.join(REF_BIN, "psearch.exe"))
+
+
+def _make(tmp, nref, nread, seed, max_patlen=600, rot=True):
+    from vntrseek_b200 import synth
+    refs = synth.make_refs(nref, seed=seed, max_patlen=max_patlen, rot_frac=0.03 if rot else 0.0)
+    reads = synth.make_reads(refs, nread, seed=seed + 100, rot_frac=0.02 if rot else 0.0)
+    refs.write_leb36(os.path.join(tmp, "reference.leb36"))
+    reads.write_leb36(os.path.join(tmp, "reads.leb36"))
+    return refs, reads
+
+
+@pytest.mark.parametrize("nref,nread,seed,maxlen", [(300, 400, 3, 200), (2000, 3000, 1, 600), (1500, 1500, 7, 2000)])
+def test_psearch_matches_reference(tmp_path, dst_file, nref, nread, seed, maxlen):
+    if not _have_ref():
+        pytest.skip("oracle/_ref/psearch.exe not built")
+    a, b = str(tmp_path / "ref"), str(tmp_path / "our")
+    os.makedirs(a)
+    _make(a, nref, nread, seed, maxlen)
+    shutil.copytree(a, b)
+    args = ["reference.leb36", "reads.leb36", dst_file, 88, 0, 50]
+    rc1, _, log1 = run(os.path.join(REF_BIN, "psearch.exe"), args, a)
+    rc2, _, log2 = run(os.path.join(OUR_BIN, "psearch.exe"), args, b)
+    assert rc1 == 0 and rc2 == 0, (rc1, rc2, log2[-500:])
+    assert parse_counters(log2) == parse_counters(log1)
+    assert canonical_clu(os.path.join(b, "reads.leb36.clu")) == canonical_clu(os.path.join(a, "reads.leb36.clu"))
+
+
+def test_psearch_golden_small(tmp_path, dst_file):
+    """committed fixture (inputs + the reference's outputs), no reference binary needed"""
+    from conftest import GOLDEN
+    g = os.path.join(GOLDEN, "psearch_small")
+    w = str(tmp_path / "w")
+    shutil.copytree(g, w)
+    os.rename(os.path.join(w, "reads.leb36.clu"), os.path.join(w, "expected.clu"))
+    rc, _, log = run(os.path.join(OUR_BIN, "psearch.exe"), ["reference.leb36", "reads.leb36", dst_file, 88, 0, 50], w)
+    assert rc == 0, log[-500:]
+    assert parse_counters(log) == parse_counters(open(os.path.join(w, "ref.log")).read())
+    assert canonical_clu(os.path.join(w, "reads.leb36.clu")) == canonical_clu(os.path.join(w, "expected.clu"))
+
+
+def test_edges_mode_byte_exact(tmp_path, dst_file):
+    if not _have_ref():
+        pytest.skip("oracle/_ref/psearch.exe not built")
+    a, b = str(tmp_path / "ref"), str(tmp_path / "our")
+    os.makedirs(a)
+    refs, reads = _make(a, 200, 300, 5, 400, rot=False)
+    rng = np.random.default_rng(0)
+    with open(os.path.join(a, "x.edgein"), "w") as f:
+        for _ in range(500):
+            f.write("%d,%d\n" % (refs.key[int(rng.integers(0, len(refs)))], reads.key[int(rng.integers(0, len(reads)))]))
+    shutil.copytree(a, b)
+    args = ["reference.leb36", "reads.leb36", dst_file, 70, 0, 0, "x.edgein"]
+    rc1, _, _ = run(os.path.join(REF_BIN, "psearch.exe"), args, a)
+    rc2, _, log2 = run(os.path.join(OUR_BIN, "psearch.exe"), args, b)
+    assert rc1 == 0 and rc2 == 0, log2[-500:]
+    assert filecmp.cmp(os.path.join(a, "reads.leb36.edges"), os.path.join(b, "reads.leb36.edges"), shallow=False)
+
+
+def test_cli_errors_match_reference(tmp_path, dst_file):
+    exe = os.path.join(OUR_BIN, "psearch.exe")
+    assert run(exe, [], str(tmp_path))[0] == 1                      # usage
+    assert run(exe, ["a", "b", dst_file, 50, 0, 50], str(tmp_path))[0] == 1   # cutoff outside 70..100
+    assert run(exe, ["a", "b", dst_file, 88, 0, 50, "-m"], str(tmp_path))[0] == 1  # -m at argv[7] is taken as edges file
+    assert run(exe, ["nofile", "nofile", dst_file, 88, 0, 50], str(tmp_path))[0] == 1

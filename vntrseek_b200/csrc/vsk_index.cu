@@ -1,0 +1,389 @@
+// Host build of the reference seed index (psearch.c:161-766 + hclust.h:98-270),
+// reproducing the reference's bucket order exactly.
+//
+// Why the order matters: a read's candidate window inside a seed bucket runs from
+// the first hit with pmin >= lo up to AND INCLUDING the first hit with pmin > hi
+// (hclust.h:380-421).  Which hit is "first" inside an equal-pmin group is decided
+// by the reference's unstable quicksort (EasyArrayQuickSort, easylife.c:884-981),
+// whose median-of-three pivots come from a fixed-state GFSR generator
+// (easylife.c:107-141) shared by all sort calls of the process.  So the sort,
+// the generator and the order in which buckets are sorted (ascending code for
+// TRANGE <= 4; the 2-key hash's walker list, doublehash.h:334-392, for the rest)
+// are restated here.  Only the identity of the first hit of every pmin group
+// survives into the device index; the rest of a bucket is a set.
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "vsk_host.hpp"
+#include "vsk_internal.cuh"
+
+static const char *kSeeds[15] = {
+    nullptr,
+    "111*1",
+    "1111*11",
+    "11111*111",
+    "11111*1111",
+    "111111*11111*11",
+    "111111*111111*11",
+    "111*11111*111*111*11",
+    "11*111*11111**11**111*11*11",
+    "11*111*11111**11**111*11*11",
+    "11*111*11111**11**111*11*11",
+    "11*111*11111**11**111*11*11",
+    "1**11***1111**11*11**1*11*11*111**11",
+    "1**11***1111**11*11**1*11*11*111**11**111",
+    "1**11***1111**11*11**1*11*11*111**11**111*1*11",
+};
+
+const vsk_seedinfo &vsk_seeds() {
+    static vsk_seedinfo si;
+    static bool init = false;
+    if (!init) {
+        memset(&si, 0, sizeof si);
+        for (int t = 1; t <= 14; ++t) {
+            const int len = (int)strlen(kSeeds[t]);
+            si.tsize[t] = len;
+            int k = 0;
+            for (int i = 0; i < len; ++i)
+                if (kSeeds[t][i] == '1') si.off[t][k++] = i - (len - 1);  // retrieve_seed_info, hclust.h:1135-1159
+            si.nones[t] = k;
+        }
+        static const int lim[14] = {6, 10, 17, 25, 30, 39, 59, 89, 134, 201, 303, 474, 715, 1111};
+        for (int p = 0; p <= 5000; ++p) {  // psearch.c:284-318
+            int t = 0;
+            for (int k = 0; k < 14; ++k)
+                if (p >= lim[k]) t = k + 1;
+            si.trange_of[p] = (int16_t)t;
+            si.err_of[p] = (int16_t)(int)(p * 0.10 + 1.0);  // PATLEN_SIZE_ERR_FRACTION, TRUNC_ROUND_CEIL
+        }
+        init = true;
+    }
+    return si;
+}
+
+// ---- the reference's generator and sort, restated -----------------------------
+namespace {
+struct Gfsr {
+    uint32_t s[99];
+    Gfsr() {
+        static const uint32_t init[99] = {
+            40, 1387256442, 539505633, 7126687, 2115653676, 480642437, 1403109719, 898019591, 1609472695,
+            742049136, 964528840, 1774590149, 531014893, 1478060509, 224730595, 1413365137, 1415397063,
+            370513614, 1981855272, 1672294721, 1559669404, 1992066581, 440083042, 1552169384, 949029171,
+            1848294689, 1014369863, 1226252978, 199445637, 552539314, 101995811, 1795618857, 1468200845,
+            403608434, 466262418, 1783034892, 2125486341, 1437171068, 839437811, 685760609, 311739045,
+            1876584692, 223544964, 667792106, 1829604735, 887026472, 688815796, 1153871680, 1135467106,
+            1975710098, 1393037901, 330755675, 804762632, 393596594, 1695657725, 50479950, 1039358666,
+            1885424316, 400881551, 142829986, 187416368, 821029919, 1292641081, 415120294, 1104581275,
+            1258423968, 304285054, 400491932, 2014625087, 1619263031, 750624285, 1996732699, 97476312,
+            1250544934, 2145510054, 1510875684, 262891578, 616032534, 1316668730, 1500747974, 2138561534,
+            809719156, 1605036043, 510086967, 317411066, 54278455, 2052774305, 439191668, 1881943474,
+            1397167115, 2046084812, 644321591, 328615697, 1004646018, 1110120728, 2007784487, 992677826,
+            1756605308, 796797739};
+        memcpy(s, init, sizeof s);
+    }
+    double next() {
+        uint32_t p = s[0];
+        if (++p > 98) p = 1;
+        uint32_t k = p + 27;
+        if (k > 98) k -= 98;
+        s[p] ^= s[k];
+        s[0] = p;
+        return (double)s[p] / 2147483647.0;
+    }
+    int range(int lo, int hi) {  // EASYLIFE_INT_RANDRANGE + _el_roundG
+        const double d = next() * (hi - lo + 1) + lo - .5;
+        int i = (int)d;
+        const double g = d - i;
+        if (g >= .5) i++;
+        else if (g <= -.5) i--;
+        if (i < lo) i = lo;
+        if (i > hi) i = hi;
+        return i;
+    }
+};
+
+struct SortItem {
+    int16_t pmin;
+    int32_t prof;
+};
+
+struct EasySort {
+    Gfsr rng;
+    static void insertion(SortItem *a, int n) {
+        for (int j = 1; j < n; ++j) {
+            const SortItem key = a[j];
+            int i = j - 1;
+            while (i >= 0 && a[i].pmin > key.pmin) { a[i + 1] = a[i]; --i; }
+            a[i + 1] = key;
+        }
+    }
+    int partition(SortItem *a, int i, int k) {
+        int r0 = rng.range(i, k), r1 = rng.range(i, k), r2 = rng.range(i, k);
+        if (r0 > r1) std::swap(r0, r1);
+        if (r1 > r2) std::swap(r1, r2);
+        const int pval = a[r1].pmin;
+        --i;
+        ++k;
+        for (;;) {
+            do { --k; } while (a[k].pmin > pval);
+            do { ++i; } while (a[i].pmin < pval);
+            if (i >= k) break;
+            std::swap(a[i], a[k]);
+        }
+        return k;
+    }
+    void helper(SortItem *a, int i, int k) {
+        while (i < k) {
+            const int j = partition(a, i, k);
+            if (j - i >= 9) helper(a, i, j);
+            else insertion(a + i, j - i + 1);
+            i = j + 1;
+        }
+    }
+    void sort(SortItem *a, int n) { helper(a, 0, n - 1); }
+};
+
+inline uint32_t rjhash(uint32_t a) {  // doublehash.h:82-90
+    a = (a + 0x7ed55d16) + (a << 12);
+    a = (a ^ 0xc761c23c) ^ (a >> 19);
+    a = (a + 0x165667b1) + (a << 5);
+    a = (a + 0xd3a2646c) ^ (a << 9);
+    a = (a + 0xfd7046c5) + (a << 3);
+    a = (a ^ 0xb55a4f09) ^ (a >> 16);
+    return a;
+}
+
+// open-addressing map (trange, code) -> dense bucket id in creation order
+struct BucketMap {
+    std::vector<uint64_t> keys;
+    std::vector<int32_t> vals;
+    std::vector<uint8_t> tr;
+    size_t mask = 0, used = 0;
+    void init(size_t cap) {
+        size_t c = 1;
+        while (c < cap) c <<= 1;
+        keys.assign(c, 0);
+        vals.assign(c, -1);
+        tr.assign(c, 0);
+        mask = c - 1;
+        used = 0;
+    }
+    void grow() {
+        std::vector<uint64_t> ok;
+        std::vector<int32_t> ov;
+        std::vector<uint8_t> ot;
+        ok.swap(keys); ov.swap(vals); ot.swap(tr);
+        init(ok.size() * 2);
+        for (size_t i = 0; i < ok.size(); ++i)
+            if (ov[i] >= 0) { bool nw; *find(ot[i], ok[i], nw) = ov[i]; }
+    }
+    int32_t *find(int t, uint64_t code, bool &is_new) {
+        if ((used + 1) * 10 > (mask + 1) * 7) grow();
+        uint64_t h = (code ^ ((uint64_t)t << 58)) * 0x9E3779B97F4A7C15ull;
+        size_t i = (size_t)(h >> 20) & mask;
+        for (;;) {
+            if (vals[i] < 0) { keys[i] = code; tr[i] = (uint8_t)t; is_new = true; ++used; return &vals[i]; }
+            if (keys[i] == code && tr[i] == t) { is_new = false; return &vals[i]; }
+            i = (i + 1) & mask;
+        }
+    }
+};
+
+inline int base_index(char c) {
+    switch (c) {
+        case 'A': return 0;
+        case 'C': return 1;
+        case 'G': return 2;
+        case 'T': return 3;
+    }
+    return -1;
+}
+}  // namespace
+
+// seed code of the window that ends at position i (hclust.h:157-205): the first
+// 15 ones go to seedcode (high word), the rest to seedcode2 (low word)
+static inline uint64_t seed_code(const char *seq, int i, const vsk_seedinfo &si, int t) {
+    uint32_t c1 = 0, c2 = 0;
+    for (int k = 0; k < si.nones[t]; ++k) {
+        const int b = base_index(seq[i + si.off[t][k]]);
+        if (k <= 14) c1 = c1 * 4 + (uint32_t)b;
+        else c2 = c2 * 4 + (uint32_t)b;
+    }
+    return ((uint64_t)c1 << 32) | c2;
+}
+
+int vsk_build_refindex_host(const vsk_trset &refs, vsk_refindex_host &out, std::string &err) {
+    const vsk_seedinfo &si = vsk_seeds();
+    struct Bucket {
+        int t;
+        uint64_t code;
+        int64_t count = 0, start = 0, fill = 0;
+    };
+    std::vector<Bucket> buckets;
+    std::vector<int32_t> hit_bucket;  // per hit, in insertion order
+    std::vector<SortItem> hit_item;
+    BucketMap map;
+    map.init(1 << 20);
+    uint64_t tuples = 0;
+
+    auto seed_sequence = [&](int32_t prof, int t, int pmin) {
+        const char *seq = refs.cons.data() + refs.cons_off[prof];
+        const int len = (int)(refs.cons_off[prof + 1] - refs.cons_off[prof]);
+        const int ts = si.tsize[t];
+        for (int i = ts - 1; i < len; ++i) {
+            const uint64_t code = seed_code(seq, i, si, t);
+            bool is_new;
+            int32_t *slot = map.find(t, code, is_new);
+            if (is_new) {
+                *slot = (int32_t)buckets.size();
+                Bucket b;
+                b.t = t;
+                b.code = code;
+                buckets.push_back(b);
+            }
+            buckets[(size_t)*slot].count++;
+            hit_bucket.push_back(*slot);
+            hit_item.push_back(SortItem{(int16_t)pmin, prof});
+            ++tuples;
+        }
+    };
+
+    for (int32_t r = 0; r < refs.n; ++r) {
+        const int pmin = refs.patlen[r];
+        if (pmin < 7 || pmin > 5000) {  // psearch.c:518-521
+            err = "pmin(" + std::to_string(pmin) + ") must be in 7-5000 range!";
+            return VSK_ERR_ABORT;
+        }
+        if (!refs.master[r]) continue;  // psearch.c:452-471: non-masters leave the scan list
+        const int t = si.trange_of[pmin];
+        if (t <= 0) continue;
+        for (int o = 0; o < 2; ++o) {
+            const int len = (int)(refs.cons_off[2 * r + o + 1] - refs.cons_off[2 * r + o]);
+            if (si.tsize[t] > len) {  // seqdupPlusTuple, hclust.h:866-869
+                err = "Tuple size (" + std::to_string(si.tsize[t]) + ") is larger than sequence(" +
+                      std::to_string(len) + "). Aborting!";
+                return VSK_ERR_ABORT;
+            }
+        }
+        seed_sequence(2 * r, t, pmin);
+        seed_sequence(2 * r + 1, t, pmin);
+        const int e = si.err_of[pmin];
+        const int lower = pmin - e;
+        if (lower >= 7 && si.trange_of[lower] <= t - 1) {  // psearch.c:552-577
+            for (int o = 0; o < 2; ++o)
+                if (si.tsize[t - 1] > (int)(refs.cons_off[2 * r + o + 1] - refs.cons_off[2 * r + o])) {
+                    err = "Tuple size is larger than sequence. Aborting!";
+                    return VSK_ERR_ABORT;
+                }
+            seed_sequence(2 * r, t - 1, pmin);
+            seed_sequence(2 * r + 1, t - 1, pmin);
+        }
+        const int higher = pmin + e;
+        if (higher <= 5000 && si.trange_of[higher] >= t + 1) {  // psearch.c:583-607
+            for (int o = 0; o < 2; ++o)
+                if (si.tsize[t + 1] > (int)(refs.cons_off[2 * r + o + 1] - refs.cons_off[2 * r + o])) {
+                    err = "Tuple size is larger than sequence. Aborting!";
+                    return VSK_ERR_ABORT;
+                }
+            seed_sequence(2 * r, t + 1, pmin);
+            seed_sequence(2 * r + 1, t + 1, pmin);
+        }
+    }
+
+    // scatter hits into bucket-contiguous storage, insertion order kept
+    const size_t nb = buckets.size(), nh = hit_item.size();
+    int64_t acc = 0;
+    for (size_t b = 0; b < nb; ++b) { buckets[b].start = acc; acc += buckets[b].count; }
+    std::vector<SortItem> items(nh);
+    for (size_t h = 0; h < nh; ++h) {
+        Bucket &b = buckets[(size_t)hit_bucket[h]];
+        items[(size_t)(b.start + b.fill++)] = hit_item[h];
+    }
+    std::vector<int32_t>().swap(hit_bucket);
+    std::vector<SortItem>().swap(hit_item);
+
+    // the order in which the reference sorts its buckets (psearch.c:623-648)
+    std::vector<int32_t> order;
+    order.reserve(nb);
+    {
+        std::vector<int32_t> byt[15];
+        for (size_t b = 0; b < nb; ++b) byt[buckets[b].t].push_back((int32_t)b);  // creation order
+        const size_t hsize = 1162687;  // EasyLifeGetPrime(1000000), easylife.c:1620-1645
+        for (int t = 1; t <= 14; ++t) {
+            std::vector<int32_t> &v = byt[t];
+            if (t <= 4) {
+                std::sort(v.begin(), v.end(),
+                          [&](int32_t a, int32_t b) { return buckets[(size_t)a].code < buckets[(size_t)b].code; });
+                order.insert(order.end(), v.begin(), v.end());
+            } else {
+                // walker = rack slots in reverse order of first use; chain = reverse creation order
+                std::unordered_map<uint32_t, std::vector<int32_t>> racks;
+                std::vector<uint32_t> first_use;
+                for (int32_t b : v) {
+                    const uint64_t code = buckets[(size_t)b].code;
+                    const uint32_t hk = (uint32_t)((uint32_t)(rjhash((uint32_t)(code >> 32)) + rjhash((uint32_t)code)) % hsize);
+                    auto it = racks.find(hk);
+                    if (it == racks.end()) { first_use.push_back(hk); racks[hk].push_back(b); }
+                    else it->second.push_back(b);
+                }
+                for (size_t k = first_use.size(); k-- > 0;) {
+                    const std::vector<int32_t> &chain = racks[first_use[k]];
+                    for (size_t c = chain.size(); c-- > 0;) order.push_back(chain[c]);
+                }
+            }
+        }
+    }
+    EasySort sorter;
+    for (int32_t b : order) {
+        Bucket &bk = buckets[(size_t)b];
+        if (bk.count > 1) sorter.sort(items.data() + bk.start, (int)bk.count);
+    }
+
+    // flatten: per TRANGE codes ascending; entries = distinct (pmin, prof) + multiplicity + group head
+    out = vsk_refindex_host();
+    out.tuples = tuples;
+    out.total_hits = (int64_t)nh;
+    std::vector<int32_t> byt[15];
+    for (size_t b = 0; b < nb; ++b) byt[buckets[b].t].push_back((int32_t)b);
+    std::vector<std::pair<int32_t, int32_t>> tmp;  // (prof, count) scratch
+    for (int t = 1; t <= 14; ++t) {
+        std::vector<int32_t> &v = byt[t];
+        std::sort(v.begin(), v.end(),
+                  [&](int32_t a, int32_t b) { return buckets[(size_t)a].code < buckets[(size_t)b].code; });
+        out.codes[t].reserve(v.size());
+        out.bucket_off[t].reserve(v.size() + 1);
+        for (int32_t b : v) {
+            const Bucket &bk = buckets[(size_t)b];
+            out.codes[t].push_back(bk.code);
+            out.bucket_off[t].push_back((int64_t)out.e_prof.size());
+            const SortItem *a = items.data() + bk.start;
+            int64_t g = 0, cum = 0;
+            while (g < bk.count) {
+                int64_t h = g;
+                while (h < bk.count && a[h].pmin == a[g].pmin) ++h;
+                const int32_t first = a[g].prof;
+                std::vector<int32_t> profs;
+                profs.reserve((size_t)(h - g));
+                for (int64_t k = g; k < h; ++k) profs.push_back(a[k].prof);
+                std::sort(profs.begin(), profs.end());
+                for (size_t k = 0; k < profs.size();) {
+                    size_t m = k;
+                    while (m < profs.size() && profs[m] == profs[k]) ++m;
+                    out.e_pmin.push_back(a[g].pmin);
+                    out.e_prof.push_back(profs[k]);
+                    out.e_mult.push_back((int32_t)(m - k));
+                    out.e_first.push_back(first);
+                    out.e_cum.push_back(cum);
+                    cum += (int64_t)(m - k);
+                    k = m;
+                }
+                g = h;
+            }
+        }
+        out.bucket_off[t].push_back((int64_t)out.e_prof.size());
+    }
+    return VSK_OK;
+}

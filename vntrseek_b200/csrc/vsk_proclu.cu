@@ -1,0 +1,736 @@
+// PROCLU on the device: the per-read pipeline of psearch
+// (doSearchSimilarities, reference src/psearch1.91/psearch.c:777-845;
+//  _HCLUST_find_candidates hclust.h:273-494; _HCLUST_align_candidates hclust.h:497-857)
+// as a sequence of batch stages over all reads of a chunk:
+//
+//   seeds    one warp per read profile: seed codes of the consensus -> bucket of the
+//            reference index -> window of entries by pattern size (+ the one hit
+//            past `hi`) -> (read profile, ref profile) keys
+//   dedup    radix sort + unique of the keys (candsort + the "skip same ref" test,
+//            psearch.c:101-114,820-821, hclust.h:522-526)
+//   LCS      bit-parallel LCS of the two consensus strings against
+//            min((int)(.85*shortest+.5), shortest-1)            (hclust.h:533-545)
+//   DP       full or narrowband profile alignment, heaviest pairs first (vsk_dp.cu),
+//            similarity = 1 - dsum/(255*sumw) >= cutoff/100      (hclust.h:550-593)
+//   flanks   every (ref rotlist member x read rotlist member): orientation, two
+//            edit distances, thresholds                          (hclust.h:604-697)
+//   links    accepted (refkey, readkey, dir) records, in the order the reference
+//            would have called ClusterBaseAddLink, back to the host.
+#include <cub/cub.cuh>
+
+#include <algorithm>
+
+#include "vsk_bits.cuh"
+#include "vsk_host.hpp"
+
+// ---------------------------------------------------------------- device images
+struct DevTR {
+    int32_t n = 0;
+    int64_t *prof_off = nullptr, *cons_off = nullptr, *fl_off = nullptr;
+    uint16_t *ids = nullptr;
+    uint8_t *cons = nullptr, *fl = nullptr;
+    int32_t *leftlen = nullptr, *rightlen = nullptr, *patlen = nullptr, *key = nullptr;
+    int32_t *rot_off = nullptr, *rot_mem = nullptr;
+    uint8_t *dir = nullptr, *master = nullptr;
+};
+
+struct DevIndex {
+    const uint64_t *codes[15];
+    const int64_t *boff[15];
+    int32_t ncodes[15];
+    const int16_t *e_pmin;
+    const int32_t *e_prof, *e_first;
+    const int64_t *e_gcum;  // exclusive prefix of the multiplicities over all entries (+1 element)
+};
+
+struct DevLuts {
+    const int16_t *trange_of, *err_of;  // [5001]
+    const int32_t *lcs_min;             // [VSK_MAXPROF+1]
+    const int32_t *flank_maxerr;        // [VSK_MAXPROF+1]
+};
+
+struct vsk_reads {
+    vsk_ctx *ctx = nullptr;
+    const vsk_trset *host = nullptr;
+    DevTR d;
+    std::vector<void *> allocs;
+    int64_t h2d_bytes = 0;
+};
+
+struct vsk_refs {
+    vsk_ctx *ctx = nullptr;
+    const vsk_trset *host = nullptr;
+    vsk_reads *tr = nullptr;  // device image of the TR set
+    DevIndex idx;
+    DevLuts luts;
+    std::vector<void *> allocs;
+    int64_t total_hits = 0, entries = 0;
+    double build_seconds = 0;
+};
+
+__constant__ int c_seed_off[15][32];
+__constant__ int c_tsize[15];
+__constant__ int c_nones[15];
+
+template <typename T>
+static int upload_vec(vsk_ctx *ctx, std::vector<void *> &allocs, const std::vector<T> &h, T **d,
+                      int64_t *bytes = nullptr, size_t pad = 8) {
+    VSK_CUDA(ctx, cudaMalloc((void **)d, sizeof(T) * (h.size() + pad)));
+    allocs.push_back(*d);
+    if (!h.empty())
+        VSK_CUDA(ctx, cudaMemcpyAsync(*d, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, ctx->stream));
+    if (bytes) *bytes += (int64_t)(sizeof(T) * h.size());
+    return VSK_OK;
+}
+
+static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
+    vsk_reads *r = new vsk_reads();
+    r->ctx = ctx;
+    r->host = ts;
+    r->d.n = ts->n;
+    int rc;
+    std::vector<uint8_t> cons(ts->cons.begin(), ts->cons.end()), fl(ts->fl.begin(), ts->fl.end());
+    std::vector<int32_t> rot_off((size_t)ts->n + 1, 0), rot_mem;
+    for (int32_t i = 0; i < ts->n; ++i) {
+        rot_off[(size_t)i] = (int32_t)rot_mem.size();
+        rot_mem.insert(rot_mem.end(), ts->rotlist[(size_t)i].begin(), ts->rotlist[(size_t)i].end());
+    }
+    rot_off[(size_t)ts->n] = (int32_t)rot_mem.size();
+#define UP(field, vec) \
+    if ((rc = upload_vec(ctx, r->allocs, vec, &r->d.field, &r->h2d_bytes))) { *out = r; return rc; }
+    UP(prof_off, ts->prof_off) UP(cons_off, ts->cons_off) UP(fl_off, ts->fl_off) UP(ids, ts->ids)
+    UP(cons, cons) UP(fl, fl) UP(leftlen, ts->leftlen) UP(rightlen, ts->rightlen) UP(patlen, ts->patlen)
+    UP(key, ts->key) UP(rot_off, rot_off) UP(rot_mem, rot_mem) UP(dir, ts->dir) UP(master, ts->master)
+#undef UP
+    VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *out = r;
+    return VSK_OK;
+}
+
+static void free_reads(vsk_reads *r) {
+    if (!r) return;
+    for (void *p : r->allocs) cudaFree(p);
+    delete r;
+}
+
+extern "C" int vsk_reads_upload(vsk_ctx *ctx, const vsk_trset *reads, vsk_reads **out) {
+    if (!ctx || !reads || !out) return VSK_ERR_ARG;
+    VSK_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = upload_trset(ctx, reads, out);
+    if (rc) { free_reads(*out); *out = nullptr; }
+    return rc;
+}
+
+extern "C" void vsk_reads_free(vsk_ctx *ctx, vsk_reads *r) {
+    if (ctx) cudaSetDevice(ctx->device);
+    free_reads(r);
+}
+
+extern "C" int vsk_refs_create(vsk_ctx *ctx, const vsk_trset *refs, vsk_refs **out) {
+    if (!ctx || !refs || !out) return VSK_ERR_ARG;
+    *out = nullptr;
+    VSK_CUDA(ctx, cudaSetDevice(ctx->device));
+    vsk_refindex_host hi;
+    std::string err;
+    int rc = vsk_build_refindex_host(*refs, hi, err);
+    if (rc) return vsk_fail(ctx, rc, "%s", err.c_str());
+    vsk_refs *R = new vsk_refs();
+    R->ctx = ctx;
+    R->host = refs;
+    R->total_hits = hi.total_hits;
+    R->entries = (int64_t)hi.e_prof.size();
+#define FAIL(x) do { rc = (x); if (rc) { vsk_refs_free(ctx, R); return rc; } } while (0)
+    FAIL(upload_trset(ctx, refs, &R->tr));
+    memset(&R->idx, 0, sizeof R->idx);
+    for (int t = 1; t <= 14; ++t) {
+        uint64_t *dc;
+        int64_t *db;
+        FAIL(upload_vec(ctx, R->allocs, hi.codes[t], &dc));
+        if (hi.bucket_off[t].empty()) hi.bucket_off[t].push_back(0);
+        FAIL(upload_vec(ctx, R->allocs, hi.bucket_off[t], &db));
+        R->idx.codes[t] = dc;
+        R->idx.boff[t] = db;
+        R->idx.ncodes[t] = (int32_t)hi.codes[t].size();
+    }
+    std::vector<int64_t> gcum(hi.e_mult.size() + 1, 0);
+    for (size_t i = 0; i < hi.e_mult.size(); ++i) gcum[i + 1] = gcum[i] + hi.e_mult[i];
+    int16_t *dp;
+    int32_t *dpr, *dfi;
+    int64_t *dg;
+    FAIL(upload_vec(ctx, R->allocs, hi.e_pmin, &dp));
+    FAIL(upload_vec(ctx, R->allocs, hi.e_prof, &dpr));
+    FAIL(upload_vec(ctx, R->allocs, hi.e_first, &dfi));
+    FAIL(upload_vec(ctx, R->allocs, gcum, &dg));
+    R->idx.e_pmin = dp;
+    R->idx.e_prof = dpr;
+    R->idx.e_first = dfi;
+    R->idx.e_gcum = dg;
+    // lookup tables whose entries come from double arithmetic the reference does on the host
+    const vsk_seedinfo &si = vsk_seeds();
+    std::vector<int16_t> tr(si.trange_of, si.trange_of + 5001), er(si.err_of, si.err_of + 5001);
+    std::vector<int32_t> lcsmin(VSK_MAXPROF + 1), fmax(VSK_MAXPROF + 1);
+    for (int s = 0; s <= VSK_MAXPROF; ++s) {
+        const int m = (int)(s * .85 + .5);          // LCS_CUTOFF, hclust.h:538-541
+        lcsmin[(size_t)s] = std::min(m, s - 1);
+        fmax[(size_t)s] = std::min(8, (int)(0.4 * s + .01));  // hclust.h:664-667
+    }
+    int16_t *dtr, *der;
+    int32_t *dl, *df;
+    FAIL(upload_vec(ctx, R->allocs, tr, &dtr));
+    FAIL(upload_vec(ctx, R->allocs, er, &der));
+    FAIL(upload_vec(ctx, R->allocs, lcsmin, &dl));
+    FAIL(upload_vec(ctx, R->allocs, fmax, &df));
+    R->luts.trange_of = dtr;
+    R->luts.err_of = der;
+    R->luts.lcs_min = dl;
+    R->luts.flank_maxerr = df;
+    cudaError_t e = cudaMemcpyToSymbol(c_seed_off, si.off, sizeof(si.off));
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_tsize, si.tsize, sizeof(si.tsize));
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_nones, si.nones, sizeof(si.nones));
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) {
+        vsk_refs_free(ctx, R);
+        return vsk_fail(ctx, VSK_ERR_CUDA, "refs upload: %s", cudaGetErrorString(e));
+    }
+#undef FAIL
+    *out = R;
+    return VSK_OK;
+}
+
+extern "C" void vsk_refs_free(vsk_ctx *ctx, vsk_refs *R) {
+    if (!R) return;
+    if (ctx) cudaSetDevice(ctx->device);
+    free_reads(R->tr);
+    for (void *p : R->allocs) cudaFree(p);
+    delete R;
+}
+
+extern "C" int64_t vsk_refs_seed_hits(const vsk_refs *R) { return R ? R->total_hits : 0; }
+
+// ---------------------------------------------------------------- kernels
+__device__ __forceinline__ int base_code(uint8_t c) {
+    return (c == 'C') ? 1 : (c == 'G') ? 2 : (c == 'T') ? 3 : 0;
+}
+
+// window of one seed code inside the index: distinct entries [s,e2) plus, when an
+// entry past `hi` exists, the head hit of that next pattern-size group (hclust.h:380-421)
+struct SeedWindow {
+    int64_t s, e2;
+    int extra;
+};
+
+__device__ __forceinline__ bool seed_lookup(const DevIndex &idx, int t, uint64_t code, int lo, int hi,
+                                            SeedWindow &w) {
+    const uint64_t *codes = idx.codes[t];
+    int a = 0, b = idx.ncodes[t];
+    while (a < b) {
+        const int m = (a + b) >> 1;
+        if (codes[m] < code) a = m + 1;
+        else b = m;
+    }
+    if (a >= idx.ncodes[t] || codes[a] != code) return false;
+    const int64_t bs = idx.boff[t][a], be = idx.boff[t][a + 1];
+    int64_t x = bs, y = be;
+    while (x < y) {  // first entry with pmin >= lo
+        const int64_t m = (x + y) >> 1;
+        if (idx.e_pmin[m] < lo) x = m + 1;
+        else y = m;
+    }
+    w.s = x;
+    y = be;
+    while (x < y) {  // first entry with pmin > hi
+        const int64_t m = (x + y) >> 1;
+        if (idx.e_pmin[m] <= hi) x = m + 1;
+        else y = m;
+    }
+    w.e2 = x;
+    w.extra = (x < be) ? 1 : 0;
+    if (w.s >= be) return false;  // no hit with pmin >= lo: start_hit stays NULL
+    return true;
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(256)
+vsk_seed_kernel(DevTR reads, DevIndex idx, DevLuts luts, int32_t p_begin, int32_t p_end,
+                int64_t *__restrict__ cnt_emit, unsigned long long *__restrict__ raw_total,
+                const int64_t *__restrict__ off_emit, int64_t base, uint64_t *__restrict__ keys) {
+    const int lane = threadIdx.x & 31;
+    const int32_t p = p_begin + (int32_t)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5);
+    if (p >= p_end) return;
+    const int32_t q = p >> 1;
+    int64_t emit = 0, raw = 0;
+    int t = 0;
+    const int pmin = reads.patlen[q];
+    if (reads.master[q]) t = luts.trange_of[pmin];
+    if (t > 0) {
+        const int e = luts.err_of[pmin];
+        const int lo = pmin - e, hi = pmin + e;
+        const uint8_t *seq = reads.cons + reads.cons_off[p];
+        const int len = (int)(reads.cons_off[p + 1] - reads.cons_off[p]);
+        const int ts = c_tsize[t], nones = c_nones[t];
+        int64_t wbase = FILL ? (off_emit[p] - base) : 0;
+        for (int i0 = ts - 1; i0 < len; i0 += 32) {
+            const int i = i0 + lane;
+            SeedWindow w;
+            w.s = w.e2 = 0;
+            w.extra = 0;
+            bool found = false;
+            if (i < len) {
+                uint32_t c1 = 0, c2 = 0;
+                for (int k = 0; k < nones; ++k) {
+                    const uint32_t b = (uint32_t)base_code(seq[i + c_seed_off[t][k]]);
+                    if (k <= 14) c1 = c1 * 4 + b;
+                    else c2 = c2 * 4 + b;
+                }
+                found = seed_lookup(idx, t, ((uint64_t)c1 << 32) | c2, lo, hi, w);
+            }
+            const int64_t nd = found ? (w.e2 - w.s + w.extra) : 0;
+            if (!FILL) {
+                emit += nd;
+                if (found) raw += idx.e_gcum[w.e2] - idx.e_gcum[w.s] + w.extra;
+            } else {
+                // exclusive prefix of nd over the warp
+                int64_t incl = nd;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int64_t v = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += v;
+                }
+                int64_t dst = wbase + incl - nd;
+                if (found) {
+                    const uint64_t hi32 = (uint64_t)(uint32_t)p << 32;
+                    for (int64_t k = w.s; k < w.e2; ++k) keys[dst++] = hi32 | (uint32_t)idx.e_prof[k];
+                    if (w.extra) keys[dst] = hi32 | (uint32_t)idx.e_first[w.e2];
+                }
+                wbase += __shfl_sync(0xffffffffu, incl, 31);
+            }
+        }
+    }
+    if (!FILL) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            emit += __shfl_down_sync(0xffffffffu, emit, o);
+            raw += __shfl_down_sync(0xffffffffu, raw, o);
+        }
+        if (lane == 0) {
+            cnt_emit[p - p_begin] = emit;
+            if (raw) atomicAdd(raw_total, (unsigned long long)raw);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128)
+vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__restrict__ pairs, int64_t n,
+                      uint8_t *__restrict__ flags) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
+    const int nr = (int)(refs.cons_off[h + 1] - refs.cons_off[h]);
+    const int mr = (int)(reads.cons_off[p + 1] - reads.cons_off[p]);
+    const int lcs = vsk_lcs_device(refs.cons + refs.cons_off[h], nr, reads.cons + reads.cons_off[p], mr);
+    const int shortest = min(nr, mr);
+    flags[i] = (lcs >= luts.lcs_min[shortest]) ? 1 : 0;  // hclust.h:537-545
+}
+
+// DP job per surviving pair (hclust.h:550-577) + its scheduling key
+__global__ void __launch_bounds__(128)
+vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, int64_t n, double tan_angle,
+                   vsk_dp_job *__restrict__ jobs, uint32_t *__restrict__ cost, uint8_t *__restrict__ uncertain,
+                   unsigned long long *__restrict__ stats /* [0]=cells [1]=n_uncertain [2]=max_l1 */) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
+    vsk_dp_job j;
+    j.left_off = refs.prof_off[h];
+    j.top_off = reads.prof_off[p];
+    j.l1 = (int32_t)(refs.prof_off[h + 1] - j.left_off);
+    j.l2 = (int32_t)(reads.prof_off[p + 1] - j.top_off);
+    j.out_idx = (int32_t)i;
+    j.br = -1;
+    j.svector = 0.0;
+    uint8_t unc = 0;
+    unsigned long long cells = (unsigned long long)j.l1 * (unsigned long long)j.l2;
+    if (min(refs.patlen[h >> 1], reads.patlen[p >> 1]) >= 30) {
+        const double big = (double)max(j.l1, j.l2), small = (double)min(j.l1, j.l2);
+        const double sizeerror = __dmul_rn(__dsub_rn(__ddiv_rn(big, small), 1.0), 100.0);
+        if (!(sizeerror > 100.0)) {
+            // profile.h:1752-1770.  sqrt, /, * are IEEE-exact on both sides; atan/sin may differ
+            // from the host libm in the last place, so a band radius that lands within 1e-7 of
+            // an integer is handed to the host to settle (`uncertain`).
+            const double minlen = small;
+            const double virtdiagonal = sqrt(__dmul_rn(__dmul_rn(minlen, minlen), 2.0));
+            const double topangle = atan(__ddiv_rn((double)j.l1, (double)j.l2));
+            const double midradius = __dmul_rn(tan_angle, __ddiv_rn(virtdiagonal, 2.0));
+            const double bandradius = __ddiv_rn(midradius, sin(topangle));
+            const double v = (bandradius >= 6.0) ? bandradius : 6.0;
+            j.br = (int)v + 1;
+            const double fr = v - floor(v);
+            if (v > 6.0 && (fr < 1e-7 || fr > 1.0 - 1e-7)) unc = 1;
+            j.svector = __ddiv_rn((double)j.l2, (double)j.l1);
+            cells = 0;  // band cells: sum over rows of (rend - lstart + 1), profile.h:1835-1839
+            for (int row = 1; row <= j.l1; ++row) {
+                const int center = __double2int_rz(__dmul_rn((double)row, j.svector));
+                const int a = max(1, center - j.br), b = min(j.l2, center + j.br);
+                if (b >= a) cells += (unsigned long long)(b - a + 1);
+            }
+        }
+    }
+    jobs[i] = j;
+    cost[i] = (uint32_t)(((j.l2 + 255) >> 8) * (j.l1 + 31));
+    uncertain[i] = unc;
+    atomicAdd(&stats[0], cells);
+    if (unc) atomicAdd(&stats[1], 1ull);
+    atomicMax(&stats[2], (unsigned long long)j.l1);
+}
+
+__global__ void vsk_gather_jobs_kernel(const vsk_dp_job *__restrict__ jobs, const uint32_t *__restrict__ order,
+                                       int64_t n, vsk_dp_job *__restrict__ sorted) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) sorted[i] = jobs[order[i]];
+}
+
+__global__ void vsk_iota_kernel(uint32_t *v, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = (uint32_t)i;
+}
+
+// similarity test (hclust.h:593) and number of flank checks the pair expands to (hclust.h:604-607)
+__global__ void __launch_bounds__(128)
+vsk_dp_pass_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, const vsk_dp_job *__restrict__ jobs,
+                   const int4 *__restrict__ res, int64_t n, double target, int32_t *__restrict__ nexp,
+                   unsigned long long *__restrict__ stats /* [3]=passed [4]=abort */) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int4 r = res[i];
+    const double sim = __dsub_rn(1.0, __ddiv_rn((double)r.y, __dmul_rn(255.0, (double)r.z)));
+    if (jobs[i].br >= 0 && r.w > 5000) atomicAdd(&stats[4], 1ull);  // profile.h:1960-1965 exit(1)
+    int ne = 0;
+    if (sim >= target) {
+        const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
+        const int rq = p >> 1, rr = h >> 1;
+        ne = (refs.rot_off[rr + 1] - refs.rot_off[rr]) * (reads.rot_off[rq + 1] - reads.rot_off[rq]);
+        atomicAdd(&stats[3], 1ull);
+    }
+    nexp[i] = ne;
+}
+
+__global__ void __launch_bounds__(128)
+vsk_flank_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__restrict__ pairs,
+                 const int4 *__restrict__ res, const int64_t *__restrict__ exp_off, int64_t npairs, int64_t nexp,
+                 int maxerrors, vsk_link_rec *__restrict__ recs, uint8_t *__restrict__ flags,
+                 unsigned long long *__restrict__ stats /* [5]=ED error */) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nexp) return;
+    // pair that owns expansion e: last i with exp_off[i] <= e
+    int64_t a = 0, b = npairs;
+    while (a < b) {
+        const int64_t m = (a + b) >> 1;
+        if (exp_off[m + 1] <= e) a = m + 1;
+        else b = m;
+    }
+    const int64_t i = a;
+    const int k = (int)(e - exp_off[i]);
+    const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
+    const int rq = p >> 1, rr = h >> 1;
+    const int nread = reads.rot_off[rq + 1] - reads.rot_off[rq];
+    const int ma = refs.rot_mem[refs.rot_off[rr] + k / nread];    // ref rotlist member (outer loop)
+    const int mb = reads.rot_mem[reads.rot_off[rq] + k % nread];  // read rotlist member (inner loop)
+    // hclust.h:631-651
+    const int newdir = (int)(p & 1) ^ (int)(h & 1) ^ (int)refs.dir[ma] ^ (int)reads.dir[mb];
+    const int rp = 2 * ma + newdir;  // ref_ptr: forward or rc profile of the member
+    const int dp = 2 * mb;           // read_ptr: always the member's forward profile
+    const int rl = refs.leftlen[rp], rrl = refs.rightlen[rp];
+    const int ql = reads.leftlen[dp], qr = reads.rightlen[dp];
+    const int maxl = maxerrors ? maxerrors : luts.flank_maxerr[ql];
+    const int maxr = maxerrors ? maxerrors : luts.flank_maxerr[qr];
+    const int lerr = vsk_ed_device<VSK_ED_PSEARCH>(refs.fl + refs.fl_off[2 * rp], rl,
+                                                   reads.fl + reads.fl_off[2 * dp], min(ql, rl));
+    const int rerr = vsk_ed_device<VSK_ED_PSEARCH>(refs.fl + refs.fl_off[2 * rp + 1], rrl,
+                                                   reads.fl + reads.fl_off[2 * dp + 1], min(qr, rrl));
+    if (lerr == -1 || rerr == -1) atomicAdd(&stats[5], 1ull);  // hclust.h:690-694 quits
+    vsk_link_rec r;
+    r.refkey = refs.key[ma];
+    r.readkey = reads.key[mb];
+    r.dir = newdir;
+    r.lerr = lerr;
+    r.rerr = rerr;
+    r.dsum = res[i].y;
+    r.sumw = res[i].z;
+    recs[e] = r;
+    flags[e] = (lerr <= maxl && rerr <= maxr) ? 1 : 0;
+}
+
+// ---------------------------------------------------------------- host driver
+namespace {
+struct Scratch {  // stream-ordered temporaries of one run
+    vsk_ctx *ctx;
+    std::vector<void *> ptrs;
+    explicit Scratch(vsk_ctx *c) : ctx(c) {}
+    ~Scratch() {
+        for (void *p : ptrs) cudaFreeAsync(p, ctx->stream);
+    }
+    template <typename T>
+    cudaError_t get(T **p, size_t n) {
+        cudaError_t e = cudaMallocAsync((void **)p, sizeof(T) * (n ? n : 1), ctx->stream);
+        if (e == cudaSuccess) ptrs.push_back(*p);
+        return e;
+    }
+};
+inline unsigned blocks(int64_t n, int per) { return (unsigned)((n + per - 1) / per); }
+}  // namespace
+
+struct vsk_proclu_result {
+    std::vector<vsk_link_rec> links;
+    vsk_proclu_stats stats;
+};
+
+static int g_pool_set = 0;
+
+static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const vsk_proclu_params *prm,
+                     int32_t p_begin, int32_t p_end, const int64_t *d_off_emit, int64_t base, int64_t nkeys,
+                     vsk_proclu_result *out) {
+    if (nkeys == 0) return VSK_OK;
+    cudaStream_t st = ctx->stream;
+    Scratch S(ctx);
+    const DevTR &refs = R->tr->d, &reads = Q->d;
+    uint64_t *keys, *keys2, *pairs, *pairs2;
+    int64_t *d_n;
+    unsigned long long *d_stats;
+    VSK_CUDA(ctx, S.get(&keys, (size_t)nkeys));
+    VSK_CUDA(ctx, S.get(&keys2, (size_t)nkeys));
+    VSK_CUDA(ctx, S.get(&d_n, 4));
+    VSK_CUDA(ctx, S.get(&d_stats, 8));
+    VSK_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 8 * sizeof(unsigned long long), st));
+    const int64_t nprof = p_end - p_begin;
+    vsk_seed_kernel<true><<<blocks(nprof * 32, 256), 256, 0, st>>>(reads, R->idx, R->luts, p_begin, p_end,
+                                                                   nullptr, nullptr, d_off_emit, base, keys);
+    ctx->launches++;
+    // candsort + dedup
+    int end_bit = 33;
+    while (end_bit < 64 && ((uint64_t)(uint32_t)p_end >> (end_bit - 32))) ++end_bit;
+    size_t tb = 0, tb2 = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, tb, keys, keys2, nkeys, 0, end_bit, st);
+    cub::DeviceSelect::Unique(nullptr, tb2, keys2, keys, d_n, nkeys, st);
+    tb = std::max(tb, tb2);
+    void *tmp;
+    VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb));
+    VSK_CUDA(ctx, cub::DeviceRadixSort::SortKeys(tmp, tb, keys, keys2, nkeys, 0, end_bit, st));
+    VSK_CUDA(ctx, cub::DeviceSelect::Unique(tmp, tb, keys2, keys, d_n, nkeys, st));
+    pairs = keys;
+    int64_t npairs = 0;
+    VSK_CUDA(ctx, cudaMemcpyAsync(&npairs, d_n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    VSK_CUDA(ctx, cudaStreamSynchronize(st));
+    out->stats.lcs_alignments += (uint64_t)npairs;
+    if (npairs == 0) return VSK_OK;
+    // LCS filter
+    uint8_t *flags;
+    VSK_CUDA(ctx, S.get(&flags, (size_t)npairs));
+    vsk_lcs_filter_kernel<<<blocks(npairs, 128), 128, 0, st>>>(refs, reads, R->luts, pairs, npairs, flags);
+    ctx->launches++;
+    pairs2 = keys2;
+    size_t tb3 = 0;
+    cub::DeviceSelect::Flagged(nullptr, tb3, pairs, flags, pairs2, d_n, npairs, st);
+    if (tb3 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb3)); tb = tb3; }
+    VSK_CUDA(ctx, cub::DeviceSelect::Flagged(tmp, tb, pairs, flags, pairs2, d_n, npairs, st));
+    int64_t ndp = 0;
+    VSK_CUDA(ctx, cudaMemcpyAsync(&ndp, d_n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    VSK_CUDA(ctx, cudaStreamSynchronize(st));
+    out->stats.profile_alignments += (uint64_t)ndp;
+    if (ndp == 0) return VSK_OK;
+    // DP jobs, heaviest first
+    vsk_dp_job *jobs, *sorted;
+    uint32_t *cost, *cost2, *order, *order2;
+    uint8_t *unc;
+    int4 *res;
+    VSK_CUDA(ctx, S.get(&jobs, (size_t)ndp));
+    VSK_CUDA(ctx, S.get(&sorted, (size_t)ndp));
+    VSK_CUDA(ctx, S.get(&cost, (size_t)ndp));
+    VSK_CUDA(ctx, S.get(&cost2, (size_t)ndp));
+    VSK_CUDA(ctx, S.get(&order, (size_t)ndp));
+    VSK_CUDA(ctx, S.get(&order2, (size_t)ndp));
+    VSK_CUDA(ctx, S.get(&unc, (size_t)ndp));
+    VSK_CUDA(ctx, S.get(&res, (size_t)ndp));
+    const int homology_int = (int)((prm->cutoff / 100.0) * 100);  // TARGET_HOMOLOGY_INT, psearch.c:1003
+    const double tan_angle = tan(acos(homology_int / 100.0));
+    vsk_dp_jobs_kernel<<<blocks(ndp, 128), 128, 0, st>>>(refs, reads, pairs2, ndp, tan_angle, jobs, cost, unc,
+                                                        d_stats);
+    vsk_iota_kernel<<<blocks(ndp, 256), 256, 0, st>>>(order, ndp);
+    ctx->launches += 2;
+    unsigned long long hs[8];
+    VSK_CUDA(ctx, cudaMemcpyAsync(hs, d_stats, sizeof hs, cudaMemcpyDeviceToHost, st));
+    VSK_CUDA(ctx, cudaStreamSynchronize(st));
+    if (hs[1]) {  // settle band radii the device could not decide
+        std::vector<uint8_t> hu((size_t)ndp);
+        std::vector<vsk_dp_job> hj((size_t)ndp);
+        VSK_CUDA(ctx, cudaMemcpyAsync(hu.data(), unc, (size_t)ndp, cudaMemcpyDeviceToHost, st));
+        VSK_CUDA(ctx, cudaMemcpyAsync(hj.data(), jobs, sizeof(vsk_dp_job) * (size_t)ndp, cudaMemcpyDeviceToHost, st));
+        VSK_CUDA(ctx, cudaStreamSynchronize(st));
+        for (int64_t i = 0; i < ndp; ++i)
+            if (hu[(size_t)i]) {
+                vsk_band_host(hj[(size_t)i].l1, hj[(size_t)i].l2, homology_int, &hj[(size_t)i].svector,
+                              &hj[(size_t)i].br);
+                VSK_CUDA(ctx, cudaMemcpyAsync(jobs + i, &hj[(size_t)i], sizeof(vsk_dp_job), cudaMemcpyHostToDevice, st));
+            }
+        VSK_CUDA(ctx, cudaStreamSynchronize(st));
+    }
+    out->stats.dp_cells += (int64_t)hs[0];
+    size_t tb4 = 0;
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, tb4, cost, cost2, order, order2, ndp, 0, 20, st);
+    if (tb4 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb4)); tb = tb4; }
+    VSK_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, tb, cost, cost2, order, order2, ndp, 0, 20, st));
+    vsk_gather_jobs_kernel<<<blocks(ndp, 256), 256, 0, st>>>(jobs, order2, ndp, sorted);
+    ctx->launches++;
+    int rc = vsk_dp_launch(ctx, refs.ids, reads.ids, sorted, ndp, (int32_t)hs[2], res);
+    if (rc) return rc;
+    // similarity test + flank expansion
+    int32_t *nexp;
+    int64_t *exp_off;
+    VSK_CUDA(ctx, S.get(&nexp, (size_t)ndp + 1));
+    VSK_CUDA(ctx, S.get(&exp_off, (size_t)ndp + 1));
+    VSK_CUDA(ctx, cudaMemsetAsync(nexp + ndp, 0, sizeof(int32_t), st));
+    const double target = prm->cutoff / 100.0;
+    vsk_dp_pass_kernel<<<blocks(ndp, 128), 128, 0, st>>>(refs, reads, pairs2, jobs, res, ndp, target, nexp, d_stats);
+    ctx->launches++;
+    size_t tb5 = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tb5, nexp, exp_off, ndp + 1, st);
+    if (tb5 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb5)); tb = tb5; }
+    VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, tb, nexp, exp_off, ndp + 1, st));
+    int64_t ne = 0;
+    VSK_CUDA(ctx, cudaMemcpyAsync(&ne, exp_off + ndp, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    VSK_CUDA(ctx, cudaMemcpyAsync(hs, d_stats, sizeof hs, cudaMemcpyDeviceToHost, st));
+    VSK_CUDA(ctx, cudaStreamSynchronize(st));
+    out->stats.profile_alignments_success += (uint64_t)hs[3];
+    if (hs[4]) return vsk_fail(ctx, VSK_ERR_ABORT, "ERROR! Cannot find start!");
+    if (ne == 0) return VSK_OK;
+    vsk_link_rec *recs, *recs2;
+    uint8_t *lflags;
+    VSK_CUDA(ctx, S.get(&recs, (size_t)ne));
+    VSK_CUDA(ctx, S.get(&recs2, (size_t)ne));
+    VSK_CUDA(ctx, S.get(&lflags, (size_t)ne));
+    vsk_flank_kernel<<<blocks(ne, 128), 128, 0, st>>>(refs, reads, R->luts, pairs2, res, exp_off, ndp, ne,
+                                                      prm->maxerrors, recs, lflags, d_stats);
+    ctx->launches++;
+    size_t tb6 = 0;
+    cub::DeviceSelect::Flagged(nullptr, tb6, recs, lflags, recs2, d_n, ne, st);
+    if (tb6 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb6)); tb = tb6; }
+    VSK_CUDA(ctx, cub::DeviceSelect::Flagged(tmp, tb, recs, lflags, recs2, d_n, ne, st));
+    int64_t nl = 0;
+    VSK_CUDA(ctx, cudaMemcpyAsync(&nl, d_n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    VSK_CUDA(ctx, cudaMemcpyAsync(hs, d_stats, sizeof hs, cudaMemcpyDeviceToHost, st));
+    VSK_CUDA(ctx, cudaStreamSynchronize(st));
+    if (hs[5])
+        return vsk_fail(ctx, VSK_ERR_ABORT, "Edit_Distance_multiple_word_NoEndPenaltySeq1 returned -1. Aborting!");
+    const size_t old = out->links.size();
+    out->links.resize(old + (size_t)nl);
+    if (nl)
+        VSK_CUDA(ctx, cudaMemcpyAsync(out->links.data() + old, recs2, sizeof(vsk_link_rec) * (size_t)nl,
+                                      cudaMemcpyDeviceToHost, st));
+    VSK_CUDA(ctx, cudaStreamSynchronize(st));
+    out->stats.d2h_bytes += (int64_t)(sizeof(vsk_link_rec) * (size_t)nl);
+    return VSK_OK;
+}
+
+extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q,
+                                       const vsk_proclu_params *prm, vsk_proclu_result **out) {
+    if (!ctx || !R || !Q || !prm || !out) return VSK_ERR_ARG;
+    *out = nullptr;
+    if (prm->option_r) return vsk_fail(ctx, VSK_ERR_ARG, "-r (ref-to-ref) mode is not supported by the GPU path yet");
+    VSK_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!g_pool_set) {  // keep freed stream-ordered memory in the pool between runs
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) {
+            uint64_t thr = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+        }
+        g_pool_set = 1;
+    }
+    const vsk_trset *hq = Q->host;
+    const vsk_seedinfo &si = vsk_seeds();
+    for (int32_t q = 0; q < hq->n; ++q) {  // the reference quits on these (psearch.c:784-787, hclust.h:866-869)
+        const int pmin = hq->patlen[(size_t)q];
+        if (pmin < 7 || pmin > 5000) return vsk_fail(ctx, VSK_ERR_ABORT, "pmin(%d) must be in 7-5000 range!", pmin);
+        if (!hq->master[(size_t)q]) continue;
+        const int t = si.trange_of[pmin];
+        for (int o = 0; o < 2 && t > 0; ++o) {
+            const int64_t len = hq->cons_off[(size_t)(2 * q + o + 1)] - hq->cons_off[(size_t)(2 * q + o)];
+            if (si.tsize[t] > len)
+                return vsk_fail(ctx, VSK_ERR_ABORT, "Tuple size (%d) is larger than sequence(%d). Aborting!",
+                                si.tsize[t], (int)len);
+        }
+    }
+    vsk_proclu_result *res = new vsk_proclu_result();
+    memset(&res->stats, 0, sizeof res->stats);
+    const int32_t nprof = 2 * Q->d.n;
+    if (nprof == 0) { *out = res; return VSK_OK; }
+    cudaStream_t st = ctx->stream;
+    int rc = VSK_OK;
+    {
+        Scratch S(ctx);
+        int64_t *cnt, *off;
+        unsigned long long *raw;
+        cudaError_t e;
+        if ((e = S.get(&cnt, (size_t)nprof + 1)) != cudaSuccess || (e = S.get(&off, (size_t)nprof + 1)) != cudaSuccess ||
+            (e = S.get(&raw, 1)) != cudaSuccess) {
+            delete res;
+            return vsk_fail(ctx, VSK_ERR_CUDA, "alloc: %s", cudaGetErrorString(e));
+        }
+        cudaMemsetAsync(raw, 0, sizeof(unsigned long long), st);
+        cudaMemsetAsync(cnt + nprof, 0, sizeof(int64_t), st);
+        vsk_seed_kernel<false><<<blocks((int64_t)nprof * 32, 256), 256, 0, st>>>(Q->d, R->idx, R->luts, 0, nprof, cnt,
+                                                                                raw, nullptr, 0, nullptr);
+        ctx->launches++;
+        size_t tb = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, off, nprof + 1, st);
+        void *tmp;
+        S.get((uint8_t **)&tmp, tb);
+        cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, off, nprof + 1, st);
+        std::vector<int64_t> hoff((size_t)nprof + 1);
+        unsigned long long hraw = 0;
+        cudaMemcpyAsync(hoff.data(), off, sizeof(int64_t) * ((size_t)nprof + 1), cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(&hraw, raw, sizeof hraw, cudaMemcpyDeviceToHost, st);
+        e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) {
+            delete res;
+            return vsk_fail(ctx, VSK_ERR_CUDA, "seed count: %s", cudaGetErrorString(e));
+        }
+        res->stats.candidates_considered = hraw;
+        res->stats.candidate_keys = hoff[(size_t)nprof];
+        // chunks of read profiles whose keys fit the budget
+        const int64_t budget = prm->key_budget > 0 ? prm->key_budget : (int64_t)256 << 20;
+        int32_t pb = 0;
+        while (pb < nprof && rc == VSK_OK) {
+            int32_t pe = pb + 2;
+            while (pe < nprof && hoff[(size_t)pe + 2] - hoff[(size_t)pb] <= budget) pe += 2;
+            rc = run_chunk(ctx, R, Q, prm, pb, pe, off, hoff[(size_t)pb], hoff[(size_t)pe] - hoff[(size_t)pb], res);
+            res->stats.chunks++;
+            pb = pe;
+        }
+    }
+    if (rc) { delete res; return rc; }
+    res->stats.confirmed = (uint64_t)res->links.size();
+    *out = res;
+    return VSK_OK;
+}
+
+extern "C" int vsk_proclu_run(vsk_ctx *ctx, const vsk_refs *R, const vsk_trset *reads, const vsk_proclu_params *prm,
+                              vsk_proclu_result **out) {
+    if (!ctx || !R || !reads || !out) return VSK_ERR_ARG;
+    vsk_reads *Q = nullptr;
+    int rc = vsk_reads_upload(ctx, reads, &Q);
+    if (rc) return rc;
+    const int64_t h2d = Q->h2d_bytes;
+    rc = vsk_proclu_run_resident(ctx, R, Q, prm, out);
+    if (rc == VSK_OK) (*out)->stats.h2d_bytes = h2d;
+    vsk_reads_free(ctx, Q);
+    return rc;
+}
+
+extern "C" int64_t vsk_proclu_result_links(const vsk_proclu_result *r, const vsk_link **links) {
+    if (!r) return 0;
+    if (links) *links = reinterpret_cast<const vsk_link *>(r->links.data());
+    return (int64_t)r->links.size();
+}
+extern "C" void vsk_proclu_result_stats(const vsk_proclu_result *r, vsk_proclu_stats *s) {
+    if (r && s) *s = r->stats;
+}
+extern "C" void vsk_proclu_result_free(vsk_proclu_result *r) { delete r; }
