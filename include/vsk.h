@@ -44,6 +44,14 @@ const char *vsk_last_error(const vsk_ctx *ctx);
 uint64_t vsk_launch_count(const vsk_ctx *ctx);
 int vsk_sync(vsk_ctx *ctx);
 
+/* measurement helpers: CUDA events on the library's stream; per-launch timing of
+ * the DP kernel; integer-pipe peak (IADD3/VIMNMX/IMAD chains) in Gop/s          */
+int vsk_timer_start(vsk_ctx *ctx);
+int vsk_timer_stop(vsk_ctx *ctx, float *ms);
+int vsk_profile_enable(vsk_ctx *ctx, int on);
+int vsk_profile_read(vsk_ctx *ctx, double *dp_kernel_ms, int64_t *dp_kernel_launches);
+int vsk_int_peak(vsk_ctx *ctx, double *gops);
+
 /* Reads eucledian.dst (header 777,10,5 checked) into out[501501]. */
 int vsk_load_distance_file(const char *path, uint8_t *out501501);
 
@@ -159,6 +167,7 @@ typedef struct {                          /* BLASTSTATS, hclust.h:43-51 */
     int64_t candidate_keys;               /* keys materialised before dedup          */
     int64_t chunks;
     int64_t h2d_bytes, d2h_bytes;
+    int64_t dp_alg_bytes;                 /* sum over DP pairs of 2*(L1+L2)+16 bytes  */
 } vsk_proclu_stats;
 
 typedef struct {       /* one ClusterBaseAddLink call (hclust.h:813-822), in call order */

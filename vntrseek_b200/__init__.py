@@ -4,4 +4,5 @@ The product is the C-ABI library `libvsk.so` (include/vsk.h) plus the drop-in
 `psearch` / `flankalign` front-ends in vntrseek_b200/csrc/.  This Python package
 is a thin ctypes mirror of that ABI used by the tests and bench.py.
 """
-from .api import Context, ProfileSet, VskError, pack_profiles, pack_strings  # noqa: F401
+from .api import (Context, ProfileSet, RefIndex, ResidentReads, TRSetHandle, VskError, pack_profiles,  # noqa: F401
+                  pack_strings, proclu, write_clusters)

@@ -58,3 +58,67 @@ def _declare(L):
                                 _p(np.int32), _p(np.int32), _p(np.int32)]
     L.vsk_ed_pairs.argtypes = [vp, C.c_char_p, _p(np.int64), _p(np.int32), C.c_char_p, _p(np.int64),
                                _p(np.int32), C.c_int64, C.c_int, _p(np.int32)]
+
+
+class ProcluParams(C.Structure):
+    _fields_ = [("cutoff", C.c_int32), ("maxerrors", C.c_int32), ("option_r", C.c_int32),
+                ("reserved", C.c_int32), ("key_budget", C.c_int64)]
+
+
+class ProcluStats(C.Structure):
+    _fields_ = [("candidates_considered", C.c_uint64), ("lcs_alignments", C.c_uint64),
+                ("profile_alignments", C.c_uint64), ("profile_alignments_success", C.c_uint64),
+                ("confirmed", C.c_uint64), ("dp_cells", C.c_int64), ("candidate_keys", C.c_int64),
+                ("chunks", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
+                ("dp_alg_bytes", C.c_int64)]
+
+
+LINK_DTYPE = np.dtype([("refkey", np.int32), ("readkey", np.int32), ("dir", np.int32),
+                       ("lerr", np.int32), ("rerr", np.int32), ("dsum", np.int32), ("sumw", np.int32)])
+
+
+def _declare2(L):
+    vp = C.c_void_p
+    L.vsk_trset_load_leb36.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    L.vsk_trset_from_arrays.argtypes = [C.c_int32, _p(np.int32), _p(np.int32), _p(np.int64), _p(np.uint16),
+                                        _p(np.int64), _p(np.uint8), C.c_int, C.c_int, C.c_int, C.c_int,
+                                        C.POINTER(vp)]
+    L.vsk_trset_apply_rotindex.argtypes = [vp, C.c_char_p]
+    L.vsk_trsets_check_unique.argtypes = [vp, vp, C.POINTER(C.c_int32)]
+    L.vsk_trset_size.argtypes = [vp]
+    L.vsk_trset_size.restype = C.c_int32
+    L.vsk_trset_error.argtypes = [vp]
+    L.vsk_trset_error.restype = C.c_char_p
+    L.vsk_trset_free.argtypes = [vp]
+    L.vsk_trset_free.restype = None
+    L.vsk_refs_create.argtypes = [vp, vp, C.POINTER(vp)]
+    L.vsk_refs_free.argtypes = [vp, vp]
+    L.vsk_refs_free.restype = None
+    L.vsk_refs_seed_hits.argtypes = [vp]
+    L.vsk_refs_seed_hits.restype = C.c_int64
+    L.vsk_reads_upload.argtypes = [vp, vp, C.POINTER(vp)]
+    L.vsk_reads_free.argtypes = [vp, vp]
+    L.vsk_reads_free.restype = None
+    L.vsk_proclu_run.argtypes = [vp, vp, vp, C.POINTER(ProcluParams), C.POINTER(vp)]
+    L.vsk_proclu_run_resident.argtypes = [vp, vp, vp, C.POINTER(ProcluParams), C.POINTER(vp)]
+    L.vsk_proclu_result_links.argtypes = [vp, C.POINTER(vp)]
+    L.vsk_proclu_result_links.restype = C.c_int64
+    L.vsk_proclu_result_stats.argtypes = [vp, C.POINTER(ProcluStats)]
+    L.vsk_proclu_result_stats.restype = None
+    L.vsk_proclu_result_free.argtypes = [vp]
+    L.vsk_proclu_result_free.restype = None
+    L.vsk_clusters_write.argtypes = [vp, C.c_int64, C.c_char_p, C.c_char_p, C.POINTER(C.c_uint64)]
+    L.vsk_timer_start.argtypes = [vp]
+    L.vsk_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
+    L.vsk_profile_enable.argtypes = [vp, C.c_int]
+    L.vsk_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    L.vsk_int_peak.argtypes = [vp, C.POINTER(C.c_double)]
+    L.vsk_edges_run.argtypes = [vp, vp, vp, C.c_char_p, C.c_char_p, C.POINTER(C.c_int64)]
+
+
+_declare_base = _declare
+
+
+def _declare(L):  # noqa: F811
+    _declare_base(L)
+    _declare2(L)

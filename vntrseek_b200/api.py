@@ -98,6 +98,27 @@ class Context:
     def sync(self):
         self._check(lib().vsk_sync(self.h))
 
+    def timer_start(self):
+        self._check(lib().vsk_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._check(lib().vsk_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def profile(self, on):
+        self._check(lib().vsk_profile_enable(self.h, int(on)))
+
+    def profile_read(self):
+        ms, n = C.c_double(), C.c_int64()
+        self._check(lib().vsk_profile_read(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def int_peak_gops(self):
+        g = C.c_double()
+        self._check(lib().vsk_int_peak(self.h, C.byref(g)))
+        return g.value
+
     @property
     def launches(self):
         return lib().vsk_launch_count(self.h)
@@ -145,3 +166,130 @@ class Context:
         self._check(lib().vsk_ed_pairs(self.h, tbuf, np.ascontiguousarray(toff[:-1]), tlen, pbuf,
                                        np.ascontiguousarray(poff[:-1]), plen, n, variant, out))
         return out[:n]
+
+
+# ---------------------------------------------------------------------------
+# PROCLU: TR sets, reference index, per-read scan, clustering
+# ---------------------------------------------------------------------------
+from ._lib import LINK_DTYPE, ProcluParams, ProcluStats  # noqa: E402
+
+
+class TRSetHandle:
+    """vsk_trset: one .leb36 file in host memory (vsk_trset_load_leb36 / _from_arrays)."""
+
+    def __init__(self, h):
+        self.h = h
+
+    @classmethod
+    def from_file(cls, path, is_read, maxflank=50, option_r=0, reflen=50, rotindex=True):
+        h = C.c_void_p()
+        rc = lib().vsk_trset_load_leb36(path.encode(), int(is_read), maxflank, option_r, reflen, C.byref(h))
+        if rc != 0:
+            raise VskError(f"cannot load {path} ({rc})")
+        ts = cls(h)
+        if rotindex:
+            ts.apply_rotindex(path + ".rotindex")
+        return ts
+
+    @classmethod
+    def from_packed(cls, p, is_read, maxflank=50, option_r=0, reflen=50):
+        """p: synth.PackedTRSet (or anything with the same arrays)"""
+        h = C.c_void_p()
+        rc = lib().vsk_trset_from_arrays(len(p.key), p.key, p.patlen, p.prof_off, p.ids, p.flank_off,
+                                         p.flanks, int(is_read), maxflank, option_r, reflen, C.byref(h))
+        if rc != 0:
+            raise VskError(f"vsk_trset_from_arrays failed ({rc})")
+        ts = cls(h)
+        if getattr(p, "rot", None):
+            import os
+            import tempfile
+            fd, path = tempfile.mkstemp(suffix=".rotindex")
+            with os.fdopen(fd, "w") as f:
+                for grp in p.rot:
+                    f.write(" ".join("%d%s" % (k, d) for k, d in grp) + "\n")
+            try:
+                ts.apply_rotindex(path)
+            finally:
+                os.unlink(path)
+        return ts
+
+    def apply_rotindex(self, path):
+        rc = lib().vsk_trset_apply_rotindex(self.h, path.encode())
+        if rc != 0:
+            raise VskError(lib().vsk_trset_error(self.h).decode())
+
+    def __len__(self):
+        return lib().vsk_trset_size(self.h)
+
+    def close(self):
+        if self.h:
+            lib().vsk_trset_free(self.h)
+            self.h = C.c_void_p()
+
+
+class RefIndex:
+    """vsk_refs: reference TR set + seed index resident in HBM."""
+
+    def __init__(self, ctx, trset):
+        self.ctx, self.trset = ctx, trset
+        self.h = C.c_void_p()
+        ctx._check(lib().vsk_refs_create(ctx.h, trset.h, C.byref(self.h)))
+
+    @property
+    def seed_hits(self):
+        return lib().vsk_refs_seed_hits(self.h)
+
+    def close(self):
+        if self.h:
+            lib().vsk_refs_free(self.ctx.h, self.h)
+            self.h = C.c_void_p()
+
+
+class ResidentReads:
+    def __init__(self, ctx, trset):
+        self.ctx, self.trset = ctx, trset
+        self.h = C.c_void_p()
+        ctx._check(lib().vsk_reads_upload(ctx.h, trset.h, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().vsk_reads_free(self.ctx.h, self.h)
+            self.h = C.c_void_p()
+
+
+def _stats_dict(st):
+    return {name: int(getattr(st, name)) for name, _ in ProcluStats._fields_}
+
+
+def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=True):
+    """vsk_proclu_run (reads = TRSetHandle, host buffers) or vsk_proclu_run_resident
+    (reads = ResidentReads).  Returns (links structured array, stats dict)."""
+    prm = ProcluParams(cutoff, maxerrors, 0, 0, key_budget)
+    res = C.c_void_p()
+    if isinstance(reads, ResidentReads):
+        ctx._check(lib().vsk_proclu_run_resident(ctx.h, refs.h, reads.h, C.byref(prm), C.byref(res)))
+    else:
+        ctx._check(lib().vsk_proclu_run(ctx.h, refs.h, reads.h, C.byref(prm), C.byref(res)))
+    st = ProcluStats()
+    lib().vsk_proclu_result_stats(res, C.byref(st))
+    links = None
+    if fetch_links:
+        ptr = C.c_void_p()
+        n = lib().vsk_proclu_result_links(res, C.byref(ptr))
+        if n:
+            buf = (C.c_char * (n * LINK_DTYPE.itemsize)).from_address(ptr.value)
+            links = np.frombuffer(buf, dtype=LINK_DTYPE, count=n).copy()
+        else:
+            links = np.zeros(0, LINK_DTYPE)
+    lib().vsk_proclu_result_free(res)
+    return links, _stats_dict(st)
+
+
+def write_clusters(links, clu_path, map_path=None):
+    links = np.ascontiguousarray(links, LINK_DTYPE)
+    tr = C.c_uint64()
+    rc = lib().vsk_clusters_write(links.ctypes.data_as(C.c_void_p), len(links), clu_path.encode(),
+                                  map_path.encode() if map_path else None, C.byref(tr))
+    if rc != 0:
+        raise VskError(f"vsk_clusters_write failed ({rc})")
+    return tr.value

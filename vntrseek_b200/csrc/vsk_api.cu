@@ -334,3 +334,85 @@ extern "C" int vsk_ed_pairs(vsk_ctx *ctx, const char *text, const int64_t *t_off
     cudaFree(dt); cudaFree(dp); cudaFree(dto); cudaFree(dpo); cudaFree(dtl); cudaFree(dpl); cudaFree(dout);
     return rc;
 }
+
+// ---- timing helpers (CUDA events on the library's own stream) --------------------
+extern "C" int vsk_timer_start(vsk_ctx *ctx) {
+    if (!ctx) return VSK_ERR_ARG;
+    if (!ctx->t0) {
+        VSK_CUDA(ctx, cudaEventCreate(&ctx->t0));
+        VSK_CUDA(ctx, cudaEventCreate(&ctx->t1));
+    }
+    VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    VSK_CUDA(ctx, cudaEventRecord(ctx->t0, ctx->stream));
+    return VSK_OK;
+}
+
+extern "C" int vsk_timer_stop(vsk_ctx *ctx, float *ms) {
+    if (!ctx || !ms || !ctx->t0) return VSK_ERR_ARG;
+    VSK_CUDA(ctx, cudaEventRecord(ctx->t1, ctx->stream));
+    VSK_CUDA(ctx, cudaEventSynchronize(ctx->t1));
+    VSK_CUDA(ctx, cudaEventElapsedTime(ms, ctx->t0, ctx->t1));
+    return VSK_OK;
+}
+
+extern "C" int vsk_profile_enable(vsk_ctx *ctx, int on) {
+    if (!ctx) return VSK_ERR_ARG;
+    ctx->profile = on != 0;
+    return VSK_OK;
+}
+
+extern "C" int vsk_profile_read(vsk_ctx *ctx, double *dp_ms, int64_t *dp_launches) {
+    if (!ctx) return VSK_ERR_ARG;
+    VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    double tot = 0;
+    for (size_t i = 0; i + 1 < ctx->prof_events.size(); i += 2) {
+        float ms = 0;
+        VSK_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->prof_events[i], ctx->prof_events[i + 1]));
+        tot += ms;
+        cudaEventDestroy(ctx->prof_events[i]);
+        cudaEventDestroy(ctx->prof_events[i + 1]);
+    }
+    if (dp_ms) *dp_ms = tot;
+    if (dp_launches) *dp_launches = (int64_t)(ctx->prof_events.size() / 2);
+    ctx->prof_events.clear();
+    return VSK_OK;
+}
+
+// Integer-pipe peak on this device: independent chains of IADD3 / VIMNMX / IMAD.
+__global__ void __launch_bounds__(256) vsk_int_peak_kernel(int *out, int iters, int seed) {
+    int a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = seed + threadIdx.x * (k + 1);
+    const int b = seed | 1, c = seed ^ 0x5555;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            a[k] = a[k] + b;          // IADD3
+            a[k] = min(a[k], c + i);  // VIMNMX (+ IADD on the uniform path)
+            a[k] = a[k] * 3 + k;      // IMAD
+        }
+    }
+    int s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s ^= a[k];
+    if (s == 0x7fffffff) out[0] = s;
+}
+
+extern "C" int vsk_int_peak(vsk_ctx *ctx, double *gops) {
+    if (!ctx || !gops) return VSK_ERR_ARG;
+    const int iters = 20000, grid = ctx->sm_count * 8;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        float ms;
+        int rc = vsk_timer_start(ctx);
+        if (rc) return rc;
+        vsk_int_peak_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_queue + 4, iters, rep + 1);
+        VSK_CUDA(ctx, cudaGetLastError());
+        rc = vsk_timer_stop(ctx, &ms);
+        if (rc) return rc;
+        if (rep > 0 && ms < best) best = ms;
+    }
+    // 3 integer instructions per chain step, 8 chains, 256 threads
+    *gops = 3.0 * 8 * 256 * (double)grid * iters / (best * 1e-3) / 1e9;
+    return VSK_OK;
+}

@@ -311,9 +311,20 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         ctx->dp_scratch_bytes = bytes;
     }
     VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ctx->profile) {
+        VSK_CUDA(ctx, cudaEventCreate(&e0));
+        VSK_CUDA(ctx, cudaEventCreate(&e1));
+        VSK_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+    }
     vsk_dp_kernel<<<(unsigned)grid, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
         d_left_ids, d_top_ids, d_jobs, (int)n_jobs, ctx->d_dist, ctx->d_gapnd,
         (int4 *)ctx->d_dp_scratch, stride, ctx->d_queue, d_out);
+    if (ctx->profile) {
+        VSK_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
+        ctx->prof_events.push_back(e0);
+        ctx->prof_events.push_back(e1);
+    }
     ctx->launches++;
     VSK_CUDA(ctx, cudaGetLastError());
     return VSK_OK;

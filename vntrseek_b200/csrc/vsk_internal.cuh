@@ -30,6 +30,10 @@ struct vsk_ctx {
     int *d_queue = nullptr;       // dynamic work counter
     std::string err;
     uint64_t launches = 0;        // kernels launched through this context
+    // optional per-launch timing of the DP kernel (bench.py's roofline leg)
+    bool profile = false;
+    std::vector<cudaEvent_t> prof_events;  // start/stop pairs
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
 };
 
 struct vsk_profset {

@@ -336,7 +336,7 @@ vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__r
 __global__ void __launch_bounds__(128)
 vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, int64_t n, double tan_angle,
                    vsk_dp_job *__restrict__ jobs, uint32_t *__restrict__ cost, uint8_t *__restrict__ uncertain,
-                   unsigned long long *__restrict__ stats /* [0]=cells [1]=n_uncertain [2]=max_l1 */) {
+                   unsigned long long *__restrict__ stats /* [0]=cells [1]=n_uncertain [2]=max_l1 [6]=id+result bytes */) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
@@ -379,6 +379,7 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
     cost[i] = (uint32_t)(((j.l2 + 255) >> 8) * (j.l1 + 31));
     uncertain[i] = unc;
     atomicAdd(&stats[0], cells);
+    atomicAdd(&stats[6], (unsigned long long)(2 * (j.l1 + j.l2) + 16));  // u16 ids in, one int4 out
     if (unc) atomicAdd(&stats[1], 1ull);
     atomicMax(&stats[2], (unsigned long long)j.l1);
 }
@@ -574,6 +575,7 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
         VSK_CUDA(ctx, cudaStreamSynchronize(st));
     }
     out->stats.dp_cells += (int64_t)hs[0];
+    out->stats.dp_alg_bytes += (int64_t)hs[6];
     size_t tb4 = 0;
     cub::DeviceRadixSort::SortPairsDescending(nullptr, tb4, cost, cost2, order, order2, ndp, 0, 20, st);
     if (tb4 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb4)); tb = tb4; }

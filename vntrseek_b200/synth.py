@@ -289,3 +289,285 @@ def make_reads(refs, n, seed=2, derived_frac=0.70, key0=1, rot_frac=0.01):
         s.acgt[d] = tuple(c.count(x) for x in "ACGT")
         s.rot.append([(s.key[m], "'"), (s.key[d], dirc)])
     return s
+
+
+# ---------------------------------------------------------------------------
+# Vectorised generator for the bench-scale sets (250 K refs, 1 M+ reads).
+# Same recipe as make_refs / make_reads, produced as packed arrays.
+# ---------------------------------------------------------------------------
+_PURE = np.array([COMP_LUT[tuple(10 if k == b else 0 for k in range(4))] for b in range(4)], np.int32)
+_MIX = np.zeros((4, 4, 4), np.int32)   # [base][other][minor]
+_DASH = np.zeros((4, 5), np.int32)     # [base][ndash]
+for _b in range(4):
+    for _o in range(4):
+        for _m in range(1, 4):
+            if _o != _b:
+                _c = [0, 0, 0, 0]
+                _c[_b] = 10 - _m
+                _c[_o] = _m
+                _MIX[_b, _o, _m] = COMP_LUT[tuple(_c)]
+    for _k in range(1, 5):
+        _c = [0, 0, 0, 0]
+        _c[_b] = 10 - _k
+        _DASH[_b, _k] = COMP_LUT[tuple(_c)]
+_ASCII = np.frombuffer(b"ACGT", np.uint8)
+_COMP_ASCII = np.arange(256, dtype=np.uint8)
+for _x, _y in zip(b"ACGTN", b"TGCAN"):
+    _COMP_ASCII[_x] = _y
+
+
+class PackedTRSet:
+    """TR records as flat arrays, in the layout vsk_trset_from_arrays takes."""
+
+    def __init__(self, key, patlen, prof_off, ids, flank_off, flanks, rot=()):
+        self.key = np.ascontiguousarray(key, np.int32)
+        self.patlen = np.ascontiguousarray(patlen, np.int32)
+        self.prof_off = np.ascontiguousarray(prof_off, np.int64)    # [2n+1]
+        self.ids = np.ascontiguousarray(ids, np.uint16)
+        self.flank_off = np.ascontiguousarray(flank_off, np.int64)  # [2n+1]
+        self.flanks = np.ascontiguousarray(flanks, np.uint8)
+        self.rot = list(rot)
+
+    def __len__(self):
+        return len(self.key)
+
+    def slice(self, a, b):
+        po = self.prof_off[2 * a:2 * b + 1]
+        fo = self.flank_off[2 * a:2 * b + 1]
+        keys = set(self.key[a:b].tolist())
+        rot = [g for g in self.rot if all(k in keys for k, _ in g)]
+        return PackedTRSet(self.key[a:b], self.patlen[a:b], po - po[0], self.ids[po[0]:po[-1]],
+                           fo - fo[0], self.flanks[fo[0]:fo[-1]], rot)
+
+    def write_leb36(self, path):
+        fl = self.flanks.tobytes().decode()
+        with open(path, "w") as f:
+            for i in range(len(self)):
+                a, b, c = self.prof_off[2 * i:2 * i + 3]
+                fwd, rc = self.ids[a:b], self.ids[b:c]
+                x, y, z = self.flank_off[2 * i:2 * i + 3]
+                s = CONS_SYMBOL[fwd]
+                cnt = np.bincount(s[s != 4], minlength=4)
+                f.write("%d %d %.2f %d %d %s %s %d %d %d %d %s|%s\n" % (
+                    self.key[i], self.patlen[i], 2.5, b - a, c - b, leb36(fwd), leb36(rc),
+                    cnt[0], cnt[1], cnt[2], cnt[3], fl[x:y], fl[y:z]))
+        if self.rot:
+            with open(path + ".rotindex", "w") as f:
+                for grp in self.rot:
+                    f.write(" ".join("%d%s" % (k, d) for k, d in grp) + "\n")
+
+
+def _lengths(rng, n, max_patlen=2000):
+    u = rng.random(n)
+    L = np.where(u < .55, rng.integers(7, 31, n),
+                 np.where(u < .85, rng.integers(31, 101, n),
+                          np.where(u < .97, rng.integers(101, 401, n), rng.integers(401, 2001, n))))
+    return np.minimum(L, max_patlen).astype(np.int64)
+
+
+def _seg(L):
+    """offsets, owner index per element, position inside the segment"""
+    off = np.zeros(len(L) + 1, np.int64)
+    np.cumsum(L, out=off[1:])
+    owner = np.repeat(np.arange(len(L)), L)
+    pos = np.arange(off[-1]) - off[owner]
+    return off, owner, pos
+
+
+def _random_profiles(rng, L, lowfrac=0.20):
+    n = len(L)
+    off, owner, pos = _seg(L)
+    tot = int(off[-1])
+    bases = rng.integers(0, 4, tot)
+    low = rng.random(n) < lowfrac
+    period = rng.integers(2, 7, n)
+    units = rng.integers(0, 4, (n, 6))
+    lc = low[owner]
+    tiled = units[owner, pos % period[owner]]
+    keep = rng.random(tot) >= 0.05
+    bases = np.where(lc & keep, tiled, bases)
+    u = rng.random(tot)
+    minor = rng.integers(1, 4, tot)
+    other = (bases + rng.integers(1, 4, tot)) % 4
+    nd = rng.integers(1, 5, tot)
+    ids = np.where(u < .85, _PURE[bases], np.where(u < .97, _MIX[bases, other, minor], _DASH[bases, nd]))
+    return off, ids.astype(np.int32)
+
+
+def _rc_segments(ids, off):
+    """reverse-complement every segment"""
+    L = np.diff(off)
+    owner = np.repeat(np.arange(len(L)), L)
+    pos = np.arange(off[-1]) - off[owner]
+    src = off[owner + 1] - 1 - pos
+    return COMPLEMENT_ID[ids[src]]
+
+
+def _dna(rng, n, n_rate=0.0):
+    s = _ASCII[rng.integers(0, 4, n)]
+    if n_rate:
+        s = np.where(rng.random(n) < n_rate, np.uint8(ord("N")), s)
+    return s
+
+
+def _mutate_segments(rng, vals, off, sub, indel, newval, protect_min=0):
+    """column-wise substitutions / deletions / insertions inside segments; returns (vals, off)"""
+    L = np.diff(off)
+    owner = np.repeat(np.arange(len(L)), L)
+    tot = len(vals)
+    u = rng.random(tot)
+    cnt = np.ones(tot, np.int64)
+    cnt[u < indel / 2] = 0
+    cnt[(u >= indel / 2) & (u < indel)] = 2
+    newlen = np.bincount(owner, weights=cnt, minlength=len(L)).astype(np.int64)
+    if protect_min:
+        bad = newlen < protect_min
+        if bad.any():
+            cnt[bad[owner]] = 1
+            newlen = np.bincount(owner, weights=cnt, minlength=len(L)).astype(np.int64)
+    out = np.repeat(vals, cnt)
+    sub_src = (u >= indel) & (u < indel + sub)
+    first = np.cumsum(cnt) - cnt            # output index of each source element's first copy
+    s_idx = first[sub_src & (cnt > 0)]
+    out[s_idx] = newval(len(s_idx))
+    ins = first[cnt == 2] + 1
+    out[ins] = newval(len(ins))
+    noff = np.zeros(len(L) + 1, np.int64)
+    np.cumsum(newlen, out=noff[1:])
+    return out, noff
+
+
+def _gather_segments(vals, off, which):
+    """concatenate segments `which` of (vals, off)"""
+    L = (off[1:] - off[:-1])[which]
+    noff, owner, pos = _seg(L)
+    return vals[off[which][owner] + pos], noff
+
+
+def _assemble(key, fwd, foff, rcv, left, loff, right, roff, rot):
+    n = len(key)
+    Lf = np.diff(foff)
+    prof_len = np.empty(2 * n, np.int64)
+    prof_len[0::2] = Lf
+    prof_len[1::2] = Lf
+    prof_off = np.zeros(2 * n + 1, np.int64)
+    np.cumsum(prof_len, out=prof_off[1:])
+    ids = np.empty(int(prof_off[-1]), np.uint16)
+    _, owner, pos = _seg(Lf)
+    ids[prof_off[2 * owner] + pos] = fwd
+    ids[prof_off[2 * owner + 1] + pos] = rcv
+    fl_len = np.empty(2 * n, np.int64)
+    fl_len[0::2] = np.diff(loff)
+    fl_len[1::2] = np.diff(roff)
+    flank_off = np.zeros(2 * n + 1, np.int64)
+    np.cumsum(fl_len, out=flank_off[1:])
+    flanks = np.empty(int(flank_off[-1]), np.uint8)
+    _, o1, p1 = _seg(np.diff(loff))
+    flanks[flank_off[2 * o1] + p1] = left
+    _, o2, p2 = _seg(np.diff(roff))
+    flanks[flank_off[2 * o2 + 1] + p2] = right
+    return PackedTRSet(key, Lf.astype(np.int32), prof_off, ids, flank_off, flanks, rot)
+
+
+def fast_refs(n, seed=1, rot_frac=0.02, flank=60, max_patlen=2000):
+    """reference TR set, keys -1..-n (vectorised make_refs)"""
+    rng = np.random.default_rng(seed)
+    L = _lengths(rng, n, max_patlen)
+    off, ids = _random_profiles(rng, L)
+    rcv = _rc_segments(ids, off)
+    # redundancy groups: a duplicate takes its master's profile (or its reverse complement)
+    n_dup = int(n * rot_frac)
+    perm = rng.permutation(n)[:2 * n_dup]
+    masters, dups = perm[:n_dup], perm[n_dup:]
+    asrc = np.arange(n)
+    asrc[dups] = masters
+    flip = np.zeros(n, bool)
+    flip[dups] = rng.random(n_dup) < 0.5
+    f1, o1 = _gather_segments(ids, off, asrc)
+    r1, _ = _gather_segments(rcv, off, asrc)
+    fo, ow, _ = _seg(np.diff(o1))
+    fl = flip[ow]
+    fwd = np.where(fl, r1, f1)
+    rc = np.where(fl, f1, r1)
+    key = -(np.arange(n) + 1)
+    rot = [[(int(key[m]), "'"), (int(key[d]), '"' if flip[d] else "'")] for m, d in zip(masters, dups)]
+    loff = np.arange(n + 1, dtype=np.int64) * flank
+    left = _dna(rng, n * flank, 0.001)
+    right = _dna(rng, n * flank, 0.001)
+    return _assemble(key, fwd, o1, rc, left, loff, right, loff.copy(), rot)
+
+
+def fast_reads(refs, n, seed=2, derived_frac=0.70, key0=1, rot_frac=0.01):
+    """read TR set derived from `refs` (vectorised make_reads)"""
+    rng = np.random.default_rng(seed)
+    nref = len(refs)
+    derived = rng.random(n) < derived_frac
+    src = rng.integers(0, nref, n)
+    # forward profiles of the sources / fresh decoys
+    rfo = refs.prof_off[0::2]
+    rlen = (refs.prof_off[1::2] - refs.prof_off[0:-1:2])
+    Ld = rlen[src]
+    Lr = _lengths(rng, n)
+    L = np.where(derived, Ld, Lr)
+    off, owner, pos = _seg(L)
+    doff, dids = _random_profiles(rng, L)
+    srcpos = np.minimum(rfo[src][owner] + pos, len(refs.ids) - 1)
+    ids = np.where(derived[owner], refs.ids[srcpos].astype(np.int32), dids)
+    # mutate derived reads: 3 % substitutions, 1 % indels (never below 7 columns)
+    mids, moff = _mutate_segments(rng, ids, off, 0.03, 0.01, lambda k: _PURE[rng.integers(0, 4, k)], protect_min=7)
+    keepd = ~derived
+    if keepd.any():  # decoys stay as generated
+        pass
+    # (decoys were mutated too, which is harmless: they are random anyway)
+    rcv = _rc_segments(mids, moff)
+    # flanks
+    ll = rng.integers(10, 51, n)
+    rl = rng.integers(10, 51, n)
+    lo, lown, lpos = _seg(ll)
+    ro, rown, rpos = _seg(rl)
+    rfl = refs.flank_off
+    lsrc = rfl[2 * src + 1][lown] - ll[lown] + lpos          # last ll chars of the ref left flank
+    rsrc = rfl[2 * src + 1][rown] + rpos                     # first rl chars of the ref right flank
+    rand_l = _dna(rng, int(lo[-1]))
+    rand_r = _dna(rng, int(ro[-1]))
+    left = np.where(derived[lown], refs.flanks[np.clip(lsrc, 0, len(refs.flanks) - 1)], rand_l)
+    right = np.where(derived[rown], refs.flanks[np.clip(rsrc, 0, len(refs.flanks) - 1)], rand_r)
+    left, lo = _mutate_segments(rng, left, lo, 0.03, 0.005, lambda k: _ASCII[rng.integers(0, 4, k)], protect_min=5)
+    right, ro = _mutate_segments(rng, right, ro, 0.03, 0.005, lambda k: _ASCII[rng.integers(0, 4, k)], protect_min=5)
+    # half of the reads are stored in the opposite orientation
+    flip = rng.random(n) < 0.5
+    _, ow, _ = _seg(np.diff(moff))
+    fwd = np.where(flip[ow], rcv, mids)
+    rc = np.where(flip[ow], mids, rcv)
+    # revcomp(right) becomes the left flank and vice versa
+    def _revcomp_segments(v, o):
+        Lx = np.diff(o)
+        own = np.repeat(np.arange(len(Lx)), Lx)
+        p = np.arange(o[-1]) - o[own]
+        return _COMP_ASCII[v[o[own + 1] - 1 - p]]
+    rleft, rright = _revcomp_segments(right, ro), _revcomp_segments(left, lo)
+    # assemble per read: choose (left,right) or (revcomp(right), revcomp(left))
+    Ll = np.where(flip, np.diff(ro), np.diff(lo))
+    Lr2 = np.where(flip, np.diff(lo), np.diff(ro))
+    nlo, lown2, lpos2 = _seg(Ll)
+    nro, rown2, rpos2 = _seg(Lr2)
+    newleft = np.where(flip[lown2], rleft[np.minimum(ro[lown2] + lpos2, len(rleft) - 1)],
+                       left[np.minimum(lo[lown2] + lpos2, len(left) - 1)])
+    newright = np.where(flip[rown2], rright[np.minimum(lo[rown2] + rpos2, len(rright) - 1)],
+                        right[np.minimum(ro[rown2] + rpos2, len(right) - 1)])
+    key = key0 + np.arange(n)
+    # redundancy groups among the reads
+    n_dup = int(n * rot_frac)
+    perm = rng.permutation(n)[:2 * n_dup]
+    masters, dups = perm[:n_dup], perm[n_dup:]
+    asrc = np.arange(n)
+    asrc[dups] = masters
+    dflip = np.zeros(n, bool)
+    dflip[dups] = rng.random(n_dup) < 0.5
+    f1, o1 = _gather_segments(fwd, moff, asrc)
+    r1, _ = _gather_segments(rc, moff, asrc)
+    _, ow2, _ = _seg(np.diff(o1))
+    ff = np.where(dflip[ow2], r1, f1)
+    rr = np.where(dflip[ow2], f1, r1)
+    rot = [[(int(key[m]), "'"), (int(key[d]), '"' if dflip[d] else "'")] for m, d in zip(masters, dups)]
+    return _assemble(key, ff, o1, rr, newleft, nlo, newright, nro, rot)
