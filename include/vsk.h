@@ -91,6 +91,41 @@ int vsk_dp_batch_fetch(vsk_ctx *ctx, vsk_dp_batch *b, vsk_dp_result *out);
 int64_t vsk_dp_batch_cells(const vsk_dp_batch *b);
 void vsk_dp_batch_free(vsk_ctx *ctx, vsk_dp_batch *b);
 
+/* ---- pair DP without any allocation ------------------------------------------------
+ * (No counterpart in the reference: it exists for hosts of this library that cannot
+ * allocate device memory when they need an alignment -- the GPU is owned by the
+ * caller's own pool allocator, the call sits in a latency-critical section where the
+ * device-wide synchronisation of cudaMalloc/cudaFree is unacceptable, or the memory
+ * budget was fixed at start-up.)
+ * Same kernel and results as vsk_pair_dp.  The caller passes the inputs and the output
+ * as DEVICE pointers (composition ids of both profile sets, n results) and the pair
+ * descriptors as a HOST array; the boundary-column scratch, the device copy of the
+ * descriptors and the work counter live in one fixed device array inside libvsk.so
+ * (about 17.3 MiB, held by every GPU that loads the library until the process exits).
+ * Limits: at most VSK_STATIC_MAX_PAIRS pairs per call and VSK_STATIC_MAX_ROWS rows
+ * (l1, the reference-side profile) per pair; larger requests return VSK_ERR_ARG with a
+ * message and do nothing.  The call makes no cudaMalloc / cudaFree / allocating library
+ * call; it returns after the kernel has finished.
+ * The first call on a device also looks up the address of that array and sets one
+ * kernel attribute; make that first call before starting any stream capture.
+ * All calls on a device share the array and it keeps the previous call's contents (the
+ * work counter is cleared by every call): two calls that overlap on the same GPU --
+ * from two host threads or two contexts -- race; serialise them.                     */
+#define VSK_STATIC_MAX_PAIRS 32768
+#define VSK_STATIC_MAX_ROWS 2048
+typedef struct {
+    int64_t left_off, top_off; /* element offsets of the two profiles in the id arrays     */
+    int32_t l1, l2;            /* rows (reference TR profile) / columns (read TR profile)  */
+    int32_t br;                /* band radius from vsk_band_params, or -1 = full matrix    */
+    int32_t out_idx;           /* slot of this pair in d_out, 0..n-1                        */
+    double svector;            /* from vsk_band_params (ignored when br < 0)              */
+} vsk_dp_desc;
+int vsk_pair_dp_static(vsk_ctx *ctx, const uint16_t *d_left_ids, int64_t n_left_ids,
+                       const uint16_t *d_top_ids, int64_t n_top_ids, const vsk_dp_desc *pairs,
+                       int64_t n, vsk_dp_result *d_out);
+/* band geometry of GetFixedProfileAPNarrowband (profile.h:1752-1770), host libm */
+int vsk_band_params(int32_t l1, int32_t l2, int homology, double *svector, int32_t *br);
+
 /* ---- string sets (consensus sequences, flanks) -----------------------------
  * ASCII, concatenated; off[n+1] byte offsets.                                */
 

@@ -60,6 +60,11 @@ def _declare(L):
                                _p(np.int32), C.c_int64, C.c_int, _p(np.int32)]
 
 
+class DpDesc(C.Structure):
+    _fields_ = [("left_off", C.c_int64), ("top_off", C.c_int64), ("l1", C.c_int32), ("l2", C.c_int32),
+                ("br", C.c_int32), ("out_idx", C.c_int32), ("svector", C.c_double)]
+
+
 class ProcluParams(C.Structure):
     _fields_ = [("cutoff", C.c_int32), ("maxerrors", C.c_int32), ("option_r", C.c_int32),
                 ("reserved", C.c_int32), ("key_budget", C.c_int64)]
@@ -113,6 +118,8 @@ def _declare2(L):
     L.vsk_profile_enable.argtypes = [vp, C.c_int]
     L.vsk_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     L.vsk_int_peak.argtypes = [vp, C.POINTER(C.c_double)]
+    L.vsk_pair_dp_static.argtypes = [vp, vp, C.c_int64, vp, C.c_int64, C.POINTER(DpDesc), C.c_int64, vp]
+    L.vsk_band_params.argtypes = [C.c_int32, C.c_int32, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int32)]
     L.vsk_edges_run.argtypes = [vp, vp, vp, C.c_char_p, C.c_char_p, C.POINTER(C.c_int64)]
 
 

@@ -329,3 +329,88 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
     VSK_CUDA(ctx, cudaGetLastError());
     return VSK_OK;
 }
+
+// ---- pair DP for callers that must not allocate -------------------------------------
+// Some hosts of this library cannot call cudaMalloc at the point where they need an
+// alignment: a service that has handed the whole GPU to its own pool allocator, a
+// latency-critical section between two of the caller's launches where the implicit
+// device synchronisation of cudaMalloc/cudaFree is not acceptable, or a process whose
+// memory budget was fixed at start-up.  vsk_pair_dp_static runs the same kernel as
+// vsk_pair_dp, but everything that call would allocate (the boundary-column scratch of
+// the column strips, the device copy of the pair descriptors, the work counter) lives
+// in one file-scope device array of fixed size that every GPU loading libvsk.so holds
+// until the process exits.
+#define VSK_STATIC_CTAS 128
+
+struct VskStaticScratch {
+    int4 boundary[(size_t)VSK_STATIC_CTAS * DP_WARPS * VSK_STATIC_MAX_ROWS];  // 16 MiB
+    vsk_dp_job jobs[VSK_STATIC_MAX_PAIRS];                                    // 1.25 MiB
+    int queue[64];
+};
+static_assert(sizeof(vsk_dp_desc) == sizeof(vsk_dp_job), "public descriptor mirrors the kernel's job record");
+
+static __device__ __align__(256) unsigned char vsk_dp_static_scratch[sizeof(VskStaticScratch)];
+
+// In host code the name above is only a stand-in for the device array; the address a
+// kernel can use has to be asked for, once per device, with that device current.
+static VskStaticScratch *g_static_dev_addr[64];
+static int g_static_attr_set[64];
+
+extern "C" int vsk_pair_dp_static(vsk_ctx *ctx, const uint16_t *d_left_ids, int64_t n_left_ids,
+                                  const uint16_t *d_top_ids, int64_t n_top_ids, const vsk_dp_desc *pairs,
+                                  int64_t n, vsk_dp_result *d_out) {
+    if (!ctx || !d_left_ids || !d_top_ids || (n > 0 && (!pairs || !d_out))) return VSK_ERR_ARG;
+    if (n < 0 || n > VSK_STATIC_MAX_PAIRS)
+        return vsk_fail(ctx, VSK_ERR_ARG, "vsk_pair_dp_static: %lld pairs in one call, the fixed scratch holds %d",
+                        (long long)n, VSK_STATIC_MAX_PAIRS);
+    for (int64_t i = 0; i < n; ++i) {
+        const vsk_dp_desc &p = pairs[i];
+        if (p.l1 < 1 || p.l1 > VSK_STATIC_MAX_ROWS)
+            return vsk_fail(ctx, VSK_ERR_ARG,
+                            "vsk_pair_dp_static: pair %lld has %d rows, the fixed scratch holds %d per pair",
+                            (long long)i, p.l1, VSK_STATIC_MAX_ROWS);
+        if (p.l2 < 1 || p.l2 > VSK_MAXPROF)
+            return vsk_fail(ctx, VSK_ERR_ARG, "vsk_pair_dp_static: pair %lld has %d columns (allowed 1..%d)",
+                            (long long)i, p.l2, VSK_MAXPROF);
+        if (p.left_off < 0 || p.left_off + p.l1 > n_left_ids || p.top_off < 0 || p.top_off + p.l2 > n_top_ids ||
+            p.out_idx < 0 || p.out_idx >= n || (p.br >= 0 && !(p.svector > 0.0)))
+            return vsk_fail(ctx, VSK_ERR_ARG, "vsk_pair_dp_static: pair %lld is out of range", (long long)i);
+    }
+    if (n == 0) return VSK_OK;
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= 64) return vsk_fail(ctx, VSK_ERR_ARG, "vsk_pair_dp_static: device %d not supported", dev);
+    VSK_CUDA(ctx, cudaSetDevice(dev));
+    if (!g_static_dev_addr[dev]) {  // first call on this device: set-up (do it before any stream capture)
+        void *addr = nullptr;
+        VSK_CUDA(ctx, cudaGetSymbolAddress(&addr, vsk_dp_static_scratch));
+        g_static_dev_addr[dev] = static_cast<VskStaticScratch *>(addr);
+    }
+    if (!g_static_attr_set[dev]) {
+        VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)DP_SMEM_BYTES));
+        g_static_attr_set[dev] = 1;
+    }
+    VskStaticScratch *S = g_static_dev_addr[dev];
+    // the array keeps what the previous call left in it: the work counter must start at zero;
+    // descriptors are overwritten for [0,n); boundary cells are always written before they are read
+    VSK_CUDA(ctx, cudaMemsetAsync(S->queue, 0, sizeof(int), ctx->stream));
+    VSK_CUDA(ctx, cudaMemcpyAsync(S->jobs, pairs, sizeof(vsk_dp_job) * (size_t)n, cudaMemcpyHostToDevice,
+                                  ctx->stream));
+    int64_t grid = (n + DP_WARPS - 1) / DP_WARPS;
+    if (grid > VSK_STATIC_CTAS) grid = VSK_STATIC_CTAS;
+    vsk_dp_kernel<<<(unsigned)grid, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
+        d_left_ids, d_top_ids, S->jobs, (int)n, ctx->d_dist, ctx->d_gapnd, S->boundary, VSK_STATIC_MAX_ROWS,
+        S->queue, reinterpret_cast<int4 *>(d_out));
+    ctx->launches++;
+    VSK_CUDA(ctx, cudaGetLastError());
+    VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VSK_OK;
+}
+
+extern "C" int vsk_band_params(int32_t l1, int32_t l2, int homology, double *svector, int32_t *br) {
+    if (l1 < 1 || l2 < 1 || !svector || !br) return VSK_ERR_ARG;
+    int b = 0;
+    vsk_band_host(l1, l2, homology, svector, &b);
+    *br = b;
+    return VSK_OK;
+}

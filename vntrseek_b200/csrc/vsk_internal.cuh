@@ -59,7 +59,7 @@ int vsk_fail(vsk_ctx *ctx, int code, const char *fmt, ...);
 void vsk_band_host(int leftlen, int toplen, int homology, double *svector, int *br);
 
 // kernels / launchers -----------------------------------------------------
-struct vsk_dp_job {   // one pair as the kernel sees it (sorted by cost, heaviest first)
+struct vsk_dp_job {   // one pair as the kernel sees it (sorted by cost, heaviest first); vsk_dp_desc mirrors it
     int64_t left_off, top_off;
     int32_t l1, l2;
     int32_t br;       // band radius, <0 = full matrix
