@@ -575,6 +575,18 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
         VSK_CUDA(ctx, cudaStreamSynchronize(st));
     }
     out->stats.dp_cells += (int64_t)hs[0];
+    if (const char *dump = getenv("VSK_DUMP_JOBS")) {  // debugging aid: append (l1, l2, br) of every DP job
+        std::vector<vsk_dp_job> hj((size_t)ndp);
+        VSK_CUDA(ctx, cudaMemcpyAsync(hj.data(), jobs, sizeof(vsk_dp_job) * (size_t)ndp, cudaMemcpyDeviceToHost, st));
+        VSK_CUDA(ctx, cudaStreamSynchronize(st));
+        if (FILE *f = fopen(dump, "ab")) {
+            for (const vsk_dp_job &j : hj) {
+                const int32_t rec[3] = {j.l1, j.l2, j.br};
+                fwrite(rec, sizeof rec, 1, f);
+            }
+            fclose(f);
+        }
+    }
     out->stats.dp_alg_bytes += (int64_t)hs[6];
     size_t tb4 = 0;
     cub::DeviceRadixSort::SortPairsDescending(nullptr, tb4, cost, cost2, order, order2, ndp, 0, 20, st);
