@@ -309,6 +309,7 @@ def ours(args, rank, world, local_rank):
     wall_ms = (time.perf_counter() - t0) * 1e3
     launches = ctx.launches - l0
     dp_ms, dp_launches = ctx.profile_read()
+    stages = ctx.profile_stages()
     ctx.profile(False)
     clocks = sampler.stop()
     # ---- end-to-end leg (host buffers in, links out) ----------------------------
@@ -364,6 +365,7 @@ def ours(args, rank, world, local_rank):
             "dp_cells_per_step": cells,
             "counters_rank0": {k: stats[k] for k in ("candidates_considered", "lcs_alignments", "profile_alignments",
                                                       "profile_alignments_success", "confirmed", "chunks")},
+            "stage_ms_per_step": {k: val / K for k, val in stages.items()},
             "index_build_s": index_s, "datagen_s": gen_s, "pack_s": pack_s,
             "e2e": {"value": total_reads / (e2e_step_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": st2["h2d_bytes"], "d2h_bytes_per_step": st2["d2h_bytes"],

@@ -51,6 +51,8 @@ int vsk_timer_stop(vsk_ctx *ctx, float *ms);
 int vsk_profile_enable(vsk_ctx *ctx, int on);
 int vsk_profile_read(vsk_ctx *ctx, double *dp_kernel_ms, int64_t *dp_kernel_launches);
 int vsk_int_peak(vsk_ctx *ctx, double *gops);
+/* profile mode: "stage=ms;..." of the PROCLU pipeline stages since the last call */
+int vsk_profile_stages(vsk_ctx *ctx, char *buf, size_t n);
 
 /* Reads eucledian.dst (header 777,10,5 checked) into out[501501]. */
 int vsk_load_distance_file(const char *path, uint8_t *out501501);
@@ -229,6 +231,32 @@ void vsk_proclu_result_free(vsk_proclu_result *r);
  * (hclust.h:818-822).  *trcount = CLUSTERBASE.trcount ("total clustered").      */
 int vsk_clusters_write(const vsk_link *links, int64_t n, const char *clu_path, const char *map_path,
                        uint64_t *trcount);
+
+/* ---- flankalign ---------------------------------------------------------------------
+ * vsk_flankalign_run = the whole of flankalign.exe after argv (reference
+ * src/newflankalign/flankalign.c:288-823): parse the `.flanks` blocks, order reads and
+ * references of a block by pattern size with the reference's own sort, enumerate the
+ * read x reference pairs inside PATLEN_SIZE_ERR %, four edit distances per pair on the
+ * GPU (Edit_Distance_multiple_word_NoEndPenaltySeq1, newflankalign copy), thresholds,
+ * and write `<a>_<b>.map` into the current directory.                              */
+typedef struct {
+    int64_t blocks, pairs, accepted;
+    int64_t h2d_bytes, d2h_bytes;
+    double kernel_ms;
+} vsk_flank_stats;
+int vsk_flankalign_run(vsk_ctx *ctx, const char *inputfile, int maxerrors, int max_flank_considered,
+                       int patlen_size_err, int64_t pairs_per_batch, vsk_flank_stats *stats);
+
+/* The per-pair logic of flankalign.c:573-749 on explicit records: left/right are offsets
+ * into `pool` (left flanks already reversed, as FLANK.left holds them).
+ * out[i]: bits 0-7 lerr, 8-15 rerr, bit 16 accepted, bits 17/18 edit distance returned -1. */
+typedef struct {
+    int64_t left_off, right_off;
+    int32_t leftlen, rightlen;
+} vsk_flank;
+int vsk_flank_pairs(vsk_ctx *ctx, const char *pool, int64_t pool_bytes, const vsk_flank *refs, int32_t nref,
+                    const vsk_flank *reads, int32_t nread, const int32_t *pair_read, const int32_t *pair_ref,
+                    int64_t npairs, int maxerrors, uint32_t *out, float *kernel_ms);
 
 /* Edges mode (doEdgesBruteForce, psearch.c:1223-1405): `id1,id2` lines in, one
  * `id1{'|"},id2,%.4lf` line per edge + `#ave:` out.                              */

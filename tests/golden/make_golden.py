@@ -165,3 +165,20 @@ def psearch_small():
 
 if __name__ == "__main__":
     psearch_small()
+
+
+def flankalign_small():
+    """tests/golden/flankalign_small: a small .flanks file and the .map files the reference
+    flankalign.exe (oracle/_ref, unmodified sources) wrote for it."""
+    import shutil
+    import subprocess
+    d = os.path.join(HERE, "flankalign_small")
+    os.makedirs(d, exist_ok=True)
+    synth.write_flanks(os.path.join(d, "in.flanks"), synth.make_flank_blocks(12, seed=9))
+    shutil.rmtree(os.path.join(d, "expected"), ignore_errors=True)
+    subprocess.run([os.path.join(ROOT, "oracle", "_ref", "flankalign.exe"), os.path.join(d, "expected"), "xml",
+                    os.path.join(d, "in.flanks"), "0", "50", "2", "15"], cwd=d, check=True, capture_output=True)
+
+
+if __name__ == "__main__":
+    flankalign_small()

@@ -117,6 +117,7 @@ def _declare2(L):
     L.vsk_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
     L.vsk_profile_enable.argtypes = [vp, C.c_int]
     L.vsk_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    L.vsk_profile_stages.argtypes = [vp, C.c_char_p, C.c_size_t]
     L.vsk_int_peak.argtypes = [vp, C.POINTER(C.c_double)]
     L.vsk_pair_dp_static.argtypes = [vp, vp, C.c_int64, vp, C.c_int64, C.POINTER(DpDesc), C.c_int64, vp]
     L.vsk_band_params.argtypes = [C.c_int32, C.c_int32, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int32)]

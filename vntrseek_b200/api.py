@@ -114,6 +114,11 @@ class Context:
         self._check(lib().vsk_profile_read(self.h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def profile_stages(self):
+        buf = C.create_string_buffer(4096)
+        self._check(lib().vsk_profile_stages(self.h, buf, 4096))
+        return {k: float(v) for k, v in (kv.split("=") for kv in buf.value.decode().split(";") if kv)}
+
     def int_peak_gops(self):
         g = C.c_double()
         self._check(lib().vsk_int_peak(self.h, C.byref(g)))

@@ -355,6 +355,40 @@ extern "C" int vsk_timer_stop(vsk_ctx *ctx, float *ms) {
     return VSK_OK;
 }
 
+void vsk_stage_mark(vsk_ctx *ctx, const char *name) {
+    if (!ctx->profile) return;
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, ctx->stream);
+    ctx->stage_marks.emplace_back(name, e);
+}
+
+// "stage=ms;stage=ms;..." accumulated since the last call (profile mode)
+extern "C" int vsk_profile_stages(vsk_ctx *ctx, char *buf, size_t n) {
+    if (!ctx || !buf || !n) return VSK_ERR_ARG;
+    VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    std::vector<std::pair<std::string, double>> acc;
+    for (size_t i = 1; i < ctx->stage_marks.size(); ++i) {
+        if (!ctx->stage_marks[i].first) continue;
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ctx->stage_marks[i - 1].second, ctx->stage_marks[i].second);
+        bool found = false;
+        for (auto &a : acc)
+            if (a.first == ctx->stage_marks[i].first) { a.second += ms; found = true; }
+        if (!found) acc.emplace_back(ctx->stage_marks[i].first, ms);
+    }
+    for (auto &m : ctx->stage_marks) cudaEventDestroy(m.second);
+    ctx->stage_marks.clear();
+    std::string out;
+    char tmp[96];
+    for (auto &a : acc) {
+        snprintf(tmp, sizeof tmp, "%s=%.3f;", a.first.c_str(), a.second);
+        out += tmp;
+    }
+    snprintf(buf, n, "%s", out.c_str());
+    return VSK_OK;
+}
+
 extern "C" int vsk_profile_enable(vsk_ctx *ctx, int on) {
     if (!ctx) return VSK_ERR_ARG;
     ctx->profile = on != 0;

@@ -97,7 +97,19 @@ __device__ __forceinline__ int vsk_lcs_device(const uint8_t *__restrict__ s1, in
 }
 
 // Edit_Distance_multiple_word_NoEndPenaltySeq1(text, pat, N, M), either copy.
-template <int VARIANT>
+// complement of a flank character as flankalign builds leftcp/rightcp (flankalign.c:523-526)
+__device__ __forceinline__ uint8_t vsk_comp_char(uint8_t c) {
+    switch (c) {
+        case 'A': return 'T';
+        case 'C': return 'G';
+        case 'G': return 'C';
+        case 'T': return 'A';
+    }
+    return c;
+}
+
+// COMP: the pattern is read through vsk_comp_char (complemented on the fly)
+template <int VARIANT, bool COMP = false>
 __device__ __forceinline__ int vsk_ed_device(const uint8_t *__restrict__ text, int N,
                                              const uint8_t *__restrict__ pat, int M) {
     if (M == 0) return 0;
@@ -117,7 +129,7 @@ __device__ __forceinline__ int vsk_ed_device(const uint8_t *__restrict__ text, i
                 if (j > 0) { in_sum = c_sum[i >> 6]; in_v1 = c_v1[i >> 6]; in_v0 = c_v0[i >> 6]; }
                 o_sum = o_v1 = o_v0 = 0;
             }
-            const uint64_t m = vsk_pick(peq, vsk_code(pat[i]));
+            const uint64_t m = vsk_pick(peq, vsk_code(COMP ? vsk_comp_char(pat[i]) : pat[i]));
             const uint64_t cs = (in_sum >> sh) & 1ull;
             const uint64_t mm = m | PD;
             const uint64_t ris = ~mm;

@@ -34,7 +34,12 @@ struct vsk_ctx {
     bool profile = false;
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs
     cudaEvent_t t0 = nullptr, t1 = nullptr;
+    // stage marks of the PROCLU pipeline (profile mode): name of the stage that ENDS at the event
+    std::vector<std::pair<const char *, cudaEvent_t>> stage_marks;
 };
+
+// profile mode: drop an event that closes stage `name` (nullptr = start of a run)
+void vsk_stage_mark(vsk_ctx *ctx, const char *name);
 
 struct vsk_profset {
     int32_t n = 0;

@@ -503,9 +503,11 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, S.get(&d_stats, 8));
     VSK_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 8 * sizeof(unsigned long long), st));
     const int64_t nprof = p_end - p_begin;
+    vsk_stage_mark(ctx, nullptr);
     vsk_seed_kernel<true><<<blocks(nprof * 32, 256), 256, 0, st>>>(reads, R->idx, R->luts, p_begin, p_end,
                                                                    nullptr, nullptr, d_off_emit, base, keys);
     ctx->launches++;
+    vsk_stage_mark(ctx, "seed_fill");
     // candsort + dedup
     int end_bit = 33;
     while (end_bit < 64 && ((uint64_t)(uint32_t)p_end >> (end_bit - 32))) ++end_bit;
@@ -518,6 +520,7 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, cub::DeviceRadixSort::SortKeys(tmp, tb, keys, keys2, nkeys, 0, end_bit, st));
     VSK_CUDA(ctx, cub::DeviceSelect::Unique(tmp, tb, keys2, keys, d_n, nkeys, st));
     pairs = keys;
+    vsk_stage_mark(ctx, "sort_unique");
     int64_t npairs = 0;
     VSK_CUDA(ctx, cudaMemcpyAsync(&npairs, d_n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
     VSK_CUDA(ctx, cudaStreamSynchronize(st));
@@ -533,6 +536,7 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     cub::DeviceSelect::Flagged(nullptr, tb3, pairs, flags, pairs2, d_n, npairs, st);
     if (tb3 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb3)); tb = tb3; }
     VSK_CUDA(ctx, cub::DeviceSelect::Flagged(tmp, tb, pairs, flags, pairs2, d_n, npairs, st));
+    vsk_stage_mark(ctx, "lcs_filter");
     int64_t ndp = 0;
     VSK_CUDA(ctx, cudaMemcpyAsync(&ndp, d_n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
     VSK_CUDA(ctx, cudaStreamSynchronize(st));
@@ -594,8 +598,10 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, tb, cost, cost2, order, order2, ndp, 0, 20, st));
     vsk_gather_jobs_kernel<<<blocks(ndp, 256), 256, 0, st>>>(jobs, order2, ndp, sorted);
     ctx->launches++;
+    vsk_stage_mark(ctx, "dp_schedule");
     int rc = vsk_dp_launch(ctx, refs.ids, reads.ids, sorted, ndp, (int32_t)hs[2], res);
     if (rc) return rc;
+    vsk_stage_mark(ctx, "dp_kernel");
     // similarity test + flank expansion
     int32_t *nexp;
     int64_t *exp_off;
@@ -634,6 +640,7 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, cudaStreamSynchronize(st));
     if (hs[5])
         return vsk_fail(ctx, VSK_ERR_ABORT, "Edit_Distance_multiple_word_NoEndPenaltySeq1 returned -1. Aborting!");
+    vsk_stage_mark(ctx, "flank_links");
     const size_t old = out->links.size();
     out->links.resize(old + (size_t)nl);
     if (nl)
@@ -688,6 +695,7 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
             delete res;
             return vsk_fail(ctx, VSK_ERR_CUDA, "alloc: %s", cudaGetErrorString(e));
         }
+        vsk_stage_mark(ctx, nullptr);
         cudaMemsetAsync(raw, 0, sizeof(unsigned long long), st);
         cudaMemsetAsync(cnt + nprof, 0, sizeof(int64_t), st);
         vsk_seed_kernel<false><<<blocks((int64_t)nprof * 32, 256), 256, 0, st>>>(Q->d, R->idx, R->luts, 0, nprof, cnt,
@@ -698,6 +706,7 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         void *tmp;
         S.get((uint8_t **)&tmp, tb);
         cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, off, nprof + 1, st);
+        vsk_stage_mark(ctx, "seed_count");
         std::vector<int64_t> hoff((size_t)nprof + 1);
         unsigned long long hraw = 0;
         cudaMemcpyAsync(hoff.data(), off, sizeof(int64_t) * ((size_t)nprof + 1), cudaMemcpyDeviceToHost, st);

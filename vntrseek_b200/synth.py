@@ -571,3 +571,59 @@ def fast_reads(refs, n, seed=2, derived_frac=0.70, key0=1, rot_frac=0.01):
     rr = np.where(dflip[ow2], f1, r1)
     rot = [[(int(key[m]), "'"), (int(key[d]), '"' if dflip[d] else "'")] for m, d in zip(masters, dups)]
     return _assemble(key, ff, o1, rr, newleft, nlo, newright, nro, rot)
+
+
+# ---------------------------------------------------------------------------
+# .flanks blocks (the input of flankalign.exe, written by perl/run_flankcomp.pl:229-268)
+# ---------------------------------------------------------------------------
+def make_flank_blocks(nblocks, nref=6, nread=40, seed=5, mixed_case=True):
+    """list of (cluster, part, refs, reads); refs = (rid, dir, FL, SEQ, FR, PAT),
+    reads = (rid, dir, first, last, DNA, PAT).  Reads carry 10-70 nt of a reference's
+    flanks (mutated), half of them reverse-complemented; pattern sizes inside a block
+    spread enough that the +-15 % window matters."""
+    rng = np.random.default_rng(seed)
+    blocks = []
+    rid_read = 1
+    for b in range(nblocks):
+        base = int(rng.integers(7, 120))
+        refs = []
+        for r in range(int(rng.integers(1, nref + 1))):
+            L = max(2, int(base * rng.uniform(0.7, 1.4)))
+            pat = _rand_dna(rng, L)
+            fl, fr = _rand_dna(rng, int(rng.integers(20, 61)), 0.01), _rand_dna(rng, int(rng.integers(20, 61)), 0.01)
+            if mixed_case and rng.random() < 0.3:
+                fl = fl.lower()
+            refs.append((-(1000 * b + r + 1), "'", fl, pat * 2, fr, pat))
+        reads = []
+        for q in range(int(rng.integers(1, nread + 1))):
+            src = refs[int(rng.integers(0, len(refs)))]
+            pat = src[5]
+            if rng.random() < 0.5:
+                L = max(2, int(len(pat) * rng.uniform(0.8, 1.25)))
+                pat = _rand_dna(rng, L)
+            ll, rl = int(rng.integers(0, 71)), int(rng.integers(0, 71))
+            left = _mutate_dna(rng, src[2].upper()[-ll:] if ll else "", 0.04, 0.01)
+            right = _mutate_dna(rng, src[4].upper()[:rl], 0.04, 0.01)
+            if rng.random() < 0.3:
+                left = _rand_dna(rng, len(left))
+            rep = pat * int(rng.integers(2, 5))
+            dna = left + rep + right
+            first, last = len(left) + 1, len(left) + len(rep)
+            if rng.random() < 0.5:
+                dna = revcomp(dna.replace("N", "A"))
+                first, last = len(right) + 1, len(right) + len(rep)
+            reads.append((rid_read, '"' if rng.random() < 0.5 else "'", first, last, dna, pat))
+            rid_read += 1
+        blocks.append((b + 1, 1, refs, reads))
+    return blocks
+
+
+def write_flanks(path, blocks):
+    with open(path, "w") as f:
+        for c, h, refs, reads in blocks:
+            f.write("@(%d_%d):\n" % (c, h))
+            f.write("*" * 70 + "\n")
+            for rid, d, fl, seq, fr, pat in refs:
+                f.write("%d%s,%s,%s,%s,%s\n" % (rid, d, fl, seq, fr, pat))
+            for rid, d, first, last, dna, pat in reads:
+                f.write("%d%s,%d,%d,%s,%s\n" % (rid, d, first, last, dna, pat))
