@@ -103,7 +103,7 @@ void vsk_dp_batch_free(vsk_ctx *ctx, vsk_dp_batch *b);
  * as DEVICE pointers (composition ids of both profile sets, n results) and the pair
  * descriptors as a HOST array; the boundary-column scratch, the device copy of the
  * descriptors and the work counter live in one fixed device array inside libvsk.so
- * (about 17.3 MiB, held by every GPU that loads the library until the process exits).
+ * (about 21.3 MiB, held by every GPU that loads the library until the process exits).
  * Limits: at most VSK_STATIC_MAX_PAIRS pairs per call and VSK_STATIC_MAX_ROWS rows
  * (l1, the reference-side profile) per pair; larger requests return VSK_ERR_ARG with a
  * message and do nothing.  The call makes no cudaMalloc / cudaFree / allocating library
@@ -190,7 +190,7 @@ typedef struct {
     int32_t cutoff;      /* argv CUTOFF 70..100 (psearch.c:909-912)                  */
     int32_t maxerrors;   /* argv MAXERRORS, 0 = from flank length (hclust.h:660-668)  */
     int32_t option_r;    /* -r: not yet on the GPU path (rejected)                   */
-    int32_t reserved;
+    int32_t count_cells; /* 1: stats.dp_cells counts the reference's band cells exactly (slower) */
     int64_t key_budget;  /* candidate keys per chunk, 0 = default                    */
 } vsk_proclu_params;
 

@@ -67,7 +67,7 @@ class DpDesc(C.Structure):
 
 class ProcluParams(C.Structure):
     _fields_ = [("cutoff", C.c_int32), ("maxerrors", C.c_int32), ("option_r", C.c_int32),
-                ("reserved", C.c_int32), ("key_budget", C.c_int64)]
+                ("count_cells", C.c_int32), ("key_budget", C.c_int64)]
 
 
 class ProcluStats(C.Structure):

@@ -266,10 +266,10 @@ def _stats_dict(st):
     return {name: int(getattr(st, name)) for name, _ in ProcluStats._fields_}
 
 
-def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=True):
+def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=True, count_cells=False):
     """vsk_proclu_run (reads = TRSetHandle, host buffers) or vsk_proclu_run_resident
     (reads = ResidentReads).  Returns (links structured array, stats dict)."""
-    prm = ProcluParams(cutoff, maxerrors, 0, 0, key_budget)
+    prm = ProcluParams(cutoff, maxerrors, 0, int(count_cells), key_budget)
     res = C.c_void_p()
     if isinstance(reads, ResidentReads):
         ctx._check(lib().vsk_proclu_run_resident(ctx.h, refs.h, reads.h, C.byref(prm), C.byref(res)))

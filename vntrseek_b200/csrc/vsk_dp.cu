@@ -75,11 +75,18 @@ __device__ __forceinline__ void dp_row_cells(int (&Hd)[CPL], int (&Hp1)[CPL], in
     }
 }
 
+// Row record of the reference-side profile, built once per pair: bits 0..15 = offset of the
+// row inside the substitution table (local row index * nb, or the composition id when the
+// table is the global one), 16..23 = gap cost d(0,l), 24..31 = NONDASHES[l].
+__device__ __forceinline__ uint32_t dp_pack_row(int off, int gn) {
+    return (uint32_t)off | ((uint32_t)(gn & 255) << 16) | ((uint32_t)(gn >> 8) << 24);
+}
+
 template <int CPL, bool SMEMT>
-__device__ __forceinline__ void dp_pair(const vsk_dp_job &job, const uint16_t *__restrict__ L,
-                                     const uint16_t *__restrict__ Tp,
-                                     const uint8_t *__restrict__ dist, const uint16_t *s_gapnd,
-                                     DpWarpSmem &ws, int nb, int4 *scratch, int4 *out) {
+__device__ __forceinline__ void dp_pair(const vsk_dp_job &job, const uint16_t *__restrict__ Tp,
+                                        const uint8_t *__restrict__ dist, const uint16_t *s_gapnd,
+                                        DpWarpSmem &ws, int nb, int4 *bscr, const uint32_t *rowrec,
+                                        int4 *out) {
     const int lane = threadIdx.x & 31;
     const int l1 = job.l1, l2 = job.l2, br = job.br;
     const bool banded = br >= 0;
@@ -87,6 +94,7 @@ __device__ __forceinline__ void dp_pair(const vsk_dp_job &job, const uint16_t *_
     const int npass = (l2 + 32 * CPL - 1) / (32 * CPL);
     int totd = 0, totp1 = 0, totp2 = 0;  // row-0 prefix over the strips already done
     int Hd[CPL], Hp1[CPL], Hp2[CPL];
+    int prev_r_hi = l1;  // rows [.., prev_r_hi) of the previous strip left a boundary cell in bscr
 
     for (int pass = 0; pass < npass; ++pass) {
         const int cbase = pass * 32 * CPL + lane * CPL;  // matrix column left of this lane's strip
@@ -131,35 +139,50 @@ __device__ __forceinline__ void dp_pair(const vsk_dp_job &job, const uint16_t *_
         totp1 += __shfl_sync(FULLMASK, x1, 31);
         totp2 += __shfl_sync(FULLMASK, x2, 31);
 
+        // rows [r_lo, r_hi) (0-based) are the only ones whose band can touch this strip's columns
+        // [c0+1, c0+32*CPL]; outside them every cell of the strip is out of band.  The bounds are
+        // conservative (the per-cell mask below stays exact): center = (int)(row*sv) lies in
+        // (row*sv - 1, row*sv].
+        int r_lo = 0, r_hi = l1;
+        if (banded) {
+            const int c0 = pass * 32 * CPL;
+            const double a = (double)(c0 + 1 - br), b = (double)(min(l2, c0 + 32 * CPL) + br + 1);
+            r_lo = max(0, (int)floor(a / sv) - 2);
+            r_hi = min(l1, (int)ceil(b / sv) + 2);
+            if (r_hi < r_lo) r_hi = r_lo;
+        }
+        if (r_lo > 0) {  // the row above the first processed one is entirely out of band here
+#pragma unroll
+            for (int j = 0; j < CPL; ++j) Hd[j] = VSK_BIG;
+            dgd = VSK_BIG;
+        }
         const bool rd_scratch = (lane == 0) && (pass > 0);
         const bool wr_scratch = (lane == 31) && (pass < npass - 1);
-        int4 nxt = make_int4(0, 0, 0, 0);
-        if (rd_scratch) nxt = __ldcg(scratch);
+        int4 nxt = make_int4(VSK_BIG, 0, 0, 0);
+        if (rd_scratch && r_lo < prev_r_hi) nxt = __ldcg(bscr + r_lo);
+        // column 0 (profile.h:2084-2090) for lane 0 of the first strip is the running sum in dg*
+        uint32_t rec_next = __ldcg(rowrec + min(max(r_lo - lane, 0), l1 - 1));
 
-        const int nsteps = l1 + 31;
-        for (int s = 0; s < nsteps; ++s) {
+        auto step = [&](const int s, const bool check) {
             const int r = s - lane;  // 0-based row of the reference (left) profile
             int lfd = __shfl_up_sync(FULLMASK, Hd[CPL - 1], 1);
             int lfp1 = __shfl_up_sync(FULLMASK, Hp1[CPL - 1], 1);
             int lfp2 = __shfl_up_sync(FULLMASK, Hp2[CPL - 1], 1);
-            const bool active = (r >= 0) && (r < l1);
-            int gl = 0, ndl = 0, ri1 = 0, ri2 = 0, lo = 0, hi = CPL;
-            const uint8_t *trow = SMEMT ? ws.T : dist;
+            const bool active = !check || ((r >= r_lo) && (r < r_hi));
+            const uint32_t rec = rec_next;
+            rec_next = __ldcg(rowrec + min(max(r + 1, 0), l1 - 1));
+            const int gl = (rec >> 16) & 255, ndl = rec >> 24;
+            const int ri1 = ndl * gl, ri2 = ndl + VSK_LEN1;
+            const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
+            int lo = 0, hi = CPL;
             bool need_mask = false;
             if (active) {
-                const int id = L[r];
-                const int gn = s_gapnd[id];
-                gl = gn & 255;
-                ndl = gn >> 8;
-                ri1 = ndl * gl;
-                ri2 = ndl + VSK_LEN1;
-                trow += SMEMT ? (int)ws.mapL[id] * nb : id * VSK_DROW;
                 if (lane == 0) {
-                    if (pass == 0) {  // column 0 (profile.h:2084-2090): cumulative gap costs
+                    if (pass == 0) {
                         lfd = dgd + gl; lfp1 = dgp1 + ri1; lfp2 = dgp2 + ri2;
                     } else {
                         lfd = nxt.x; lfp1 = nxt.y; lfp2 = nxt.z;
-                        if (r + 1 < l1) nxt = __ldcg(scratch + r + 1);
+                        nxt = (r + 1 < prev_r_hi) ? __ldcg(bscr + r + 1) : make_int4(VSK_BIG, 0, 0, 0);
                     }
                 }
                 if (banded) {  // profile.h:1835-1839
@@ -180,11 +203,19 @@ __device__ __forceinline__ void dp_pair(const vsk_dp_job &job, const uint16_t *_
                     dp_row_cells<CPL, false, SMEMT>(Hd, Hp1, Hp2, tb, gt, ci1, ci2, dgd, dgp1, dgp2,
                                                     lfd, lfp1, lfp2, trow, gl, ndl, ri1, ri2, lo, hi);
                 dgd = lfd; dgp1 = lfp1; dgp2 = lfp2;
-                if (wr_scratch) scratch[r] = make_int4(Hd[CPL - 1], Hp1[CPL - 1], Hp2[CPL - 1], 0);
+                if (wr_scratch) bscr[r] = make_int4(Hd[CPL - 1], Hp1[CPL - 1], Hp2[CPL - 1], 0);
             }
-        }
+        };
+        // pipeline fill, steady state (every lane active, no range checks), drain
+        const int s_fill_end = min(r_lo + 31, r_hi + 31);
+        int s = r_lo;
+        for (; s < s_fill_end; ++s) step(s, true);
+        for (; s < r_hi; ++s) step(s, false);
+        for (; s < r_hi + 31; ++s) step(s, true);
+        prev_r_hi = r_hi;
         __syncwarp();  // scratch written by lane 31 is read by lane 0 in the next strip
     }
+    // the corner (l1, l2) is in band, so the last strip ran through row l1-1
     const int cl = (l2 - 1) - (npass - 1) * 32 * CPL;
     if (lane == cl / CPL) {
         const int jr = cl % CPL;
@@ -206,7 +237,9 @@ vsk_dp_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict_
     DpWarpSmem &ws = reinterpret_cast<DpWarpSmem *>(smem + 2048)[warp];
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_gapnd[i] = gapnd[i];
     __syncthreads();
-    int4 *my_scratch = scratch + (size_t)(blockIdx.x * DP_WARPS + warp) * scratch_stride;
+    // per-warp scratch slice: scratch_stride boundary cells (int4) followed by scratch_stride row records
+    int4 *my_bscr = scratch + (size_t)(blockIdx.x * DP_WARPS + warp) * (scratch_stride + scratch_stride / 4);
+    uint32_t *my_rowrec = reinterpret_cast<uint32_t *>(my_bscr + scratch_stride);
 
     for (;;) {
         int ji = 0;
@@ -269,10 +302,16 @@ vsk_dp_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict_
             }
             __syncwarp();
         }
+        // row records of the reference-side profile
+        for (int i = lane; i < l1; i += 32) {
+            const int id = L[i];
+            my_rowrec[i] = dp_pack_row(smemt ? (int)ws.mapL[id] * nb : id, s_gapnd[id]);
+        }
+        __syncwarp();
 #define DP_DISPATCH(CPLV)                                                                         \
     do {                                                                                          \
-        if (smemt) dp_pair<CPLV, true>(job, L, Tp, dist, s_gapnd, ws, nb, my_scratch, out);       \
-        else dp_pair<CPLV, false>(job, L, Tp, dist, s_gapnd, ws, nb, my_scratch, out);            \
+        if (smemt) dp_pair<CPLV, true>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, out);  \
+        else dp_pair<CPLV, false>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, out);       \
     } while (0)
         if (l2 <= 32) DP_DISPATCH(1);
         else if (l2 <= 64) DP_DISPATCH(2);
@@ -302,7 +341,7 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
     const int64_t need = (n_jobs + DP_WARPS - 1) / DP_WARPS;
     if (grid > need) grid = need;
     const int stride = ((max_l1 + 31) / 32) * 32;
-    const size_t bytes = (size_t)grid * DP_WARPS * stride * sizeof(int4);
+    const size_t bytes = (size_t)grid * DP_WARPS * (stride + stride / 4) * sizeof(int4);  // boundary + row records
     if (bytes > ctx->dp_scratch_bytes) {
         if (ctx->d_dp_scratch) VSK_CUDA(ctx, cudaFree(ctx->d_dp_scratch));
         ctx->d_dp_scratch = nullptr;
@@ -343,8 +382,9 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
 #define VSK_STATIC_CTAS 128
 
 struct VskStaticScratch {
-    int4 boundary[(size_t)VSK_STATIC_CTAS * DP_WARPS * VSK_STATIC_MAX_ROWS];  // 16 MiB
-    vsk_dp_job jobs[VSK_STATIC_MAX_PAIRS];                                    // 1.25 MiB
+    // per warp: VSK_STATIC_MAX_ROWS boundary cells (int4) + as many row records (uint32)
+    int4 boundary[(size_t)VSK_STATIC_CTAS * DP_WARPS * (VSK_STATIC_MAX_ROWS + VSK_STATIC_MAX_ROWS / 4)];  // 20 MiB
+    vsk_dp_job jobs[VSK_STATIC_MAX_PAIRS];  // 1.25 MiB
     int queue[64];
 };
 static_assert(sizeof(vsk_dp_desc) == sizeof(vsk_dp_job), "public descriptor mirrors the kernel's job record");

@@ -335,53 +335,73 @@ vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__r
 // DP job per surviving pair (hclust.h:550-577) + its scheduling key
 __global__ void __launch_bounds__(128)
 vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, int64_t n, double tan_angle,
+                   int count_cells,
                    vsk_dp_job *__restrict__ jobs, uint32_t *__restrict__ cost, uint8_t *__restrict__ uncertain,
                    unsigned long long *__restrict__ stats /* [0]=cells [1]=n_uncertain [2]=max_l1 [6]=id+result bytes */) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
-    vsk_dp_job j;
-    j.left_off = refs.prof_off[h];
-    j.top_off = reads.prof_off[p];
-    j.l1 = (int32_t)(refs.prof_off[h + 1] - j.left_off);
-    j.l2 = (int32_t)(reads.prof_off[p + 1] - j.top_off);
-    j.out_idx = (int32_t)i;
-    j.br = -1;
-    j.svector = 0.0;
-    uint8_t unc = 0;
-    unsigned long long cells = (unsigned long long)j.l1 * (unsigned long long)j.l2;
-    if (min(refs.patlen[h >> 1], reads.patlen[p >> 1]) >= 30) {
-        const double big = (double)max(j.l1, j.l2), small = (double)min(j.l1, j.l2);
-        const double sizeerror = __dmul_rn(__dsub_rn(__ddiv_rn(big, small), 1.0), 100.0);
-        if (!(sizeerror > 100.0)) {
-            // profile.h:1752-1770.  sqrt, /, * are IEEE-exact on both sides; atan/sin may differ
-            // from the host libm in the last place, so a band radius that lands within 1e-7 of
-            // an integer is handed to the host to settle (`uncertain`).
-            const double minlen = small;
-            const double virtdiagonal = sqrt(__dmul_rn(__dmul_rn(minlen, minlen), 2.0));
-            const double topangle = atan(__ddiv_rn((double)j.l1, (double)j.l2));
-            const double midradius = __dmul_rn(tan_angle, __ddiv_rn(virtdiagonal, 2.0));
-            const double bandradius = __ddiv_rn(midradius, sin(topangle));
-            const double v = (bandradius >= 6.0) ? bandradius : 6.0;
-            j.br = (int)v + 1;
-            const double fr = v - floor(v);
-            if (v > 6.0 && (fr < 1e-7 || fr > 1.0 - 1e-7)) unc = 1;
-            j.svector = __ddiv_rn((double)j.l2, (double)j.l1);
-            cells = 0;  // band cells: sum over rows of (rend - lstart + 1), profile.h:1835-1839
-            for (int row = 1; row <= j.l1; ++row) {
-                const int center = __double2int_rz(__dmul_rn((double)row, j.svector));
-                const int a = max(1, center - j.br), b = min(j.l2, center + j.br);
-                if (b >= a) cells += (unsigned long long)(b - a + 1);
+    unsigned long long cells = 0, bytes = 0;
+    unsigned nunc = 0;
+    int maxl1 = 0;
+    if (i < n) {
+        const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
+        vsk_dp_job j;
+        j.left_off = refs.prof_off[h];
+        j.top_off = reads.prof_off[p];
+        j.l1 = (int32_t)(refs.prof_off[h + 1] - j.left_off);
+        j.l2 = (int32_t)(reads.prof_off[p + 1] - j.top_off);
+        j.out_idx = (int32_t)i;
+        j.br = -1;
+        j.svector = 0.0;
+        uint8_t unc = 0;
+        cells = (unsigned long long)j.l1 * (unsigned long long)j.l2;
+        if (min(refs.patlen[h >> 1], reads.patlen[p >> 1]) >= 30) {
+            const double big = (double)max(j.l1, j.l2), small = (double)min(j.l1, j.l2);
+            const double sizeerror = __dmul_rn(__dsub_rn(__ddiv_rn(big, small), 1.0), 100.0);
+            if (!(sizeerror > 100.0)) {
+                // profile.h:1752-1770.  sqrt, /, * are IEEE-exact on both sides; atan/sin may differ
+                // from the host libm in the last place, so a band radius that lands within 1e-7 of
+                // an integer is handed to the host to settle (`uncertain`).
+                const double minlen = small;
+                const double virtdiagonal = sqrt(__dmul_rn(__dmul_rn(minlen, minlen), 2.0));
+                const double topangle = atan(__ddiv_rn((double)j.l1, (double)j.l2));
+                const double midradius = __dmul_rn(tan_angle, __ddiv_rn(virtdiagonal, 2.0));
+                const double bandradius = __ddiv_rn(midradius, sin(topangle));
+                const double v = (bandradius >= 6.0) ? bandradius : 6.0;
+                j.br = (int)v + 1;
+                const double fr = v - floor(v);
+                if (v > 6.0 && (fr < 1e-7 || fr > 1.0 - 1e-7)) unc = 1;
+                j.svector = __ddiv_rn((double)j.l2, (double)j.l1);
+                if (count_cells) {  // band cells: sum over rows of (rend - lstart + 1), profile.h:1835-1839
+                    cells = 0;
+                    for (int row = 1; row <= j.l1; ++row) {
+                        const int center = __double2int_rz(__dmul_rn((double)row, j.svector));
+                        const int a = max(1, center - j.br), b = min(j.l2, center + j.br);
+                        if (b >= a) cells += (unsigned long long)(b - a + 1);
+                    }
+                }
             }
         }
+        jobs[i] = j;
+        cost[i] = (uint32_t)(((j.l2 + 255) >> 8) * (j.l1 + 31));
+        uncertain[i] = unc;
+        nunc = unc;
+        maxl1 = j.l1;
+        bytes = (unsigned long long)(2 * (j.l1 + j.l2) + 16);  // u16 ids in, one int4 out
     }
-    jobs[i] = j;
-    cost[i] = (uint32_t)(((j.l2 + 255) >> 8) * (j.l1 + 31));
-    uncertain[i] = unc;
-    atomicAdd(&stats[0], cells);
-    atomicAdd(&stats[6], (unsigned long long)(2 * (j.l1 + j.l2) + 16));  // u16 ids in, one int4 out
-    if (unc) atomicAdd(&stats[1], 1ull);
-    atomicMax(&stats[2], (unsigned long long)j.l1);
+    // one atomic per warp instead of one per thread
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        cells += __shfl_down_sync(0xffffffffu, cells, o);
+        bytes += __shfl_down_sync(0xffffffffu, bytes, o);
+        nunc += __shfl_down_sync(0xffffffffu, nunc, o);
+        maxl1 = max(maxl1, __shfl_down_sync(0xffffffffu, maxl1, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&stats[0], cells);
+        if (nunc) atomicAdd(&stats[1], (unsigned long long)nunc);
+        atomicMax(&stats[2], (unsigned long long)maxl1);
+        atomicAdd(&stats[6], bytes);
+    }
 }
 
 __global__ void vsk_gather_jobs_kernel(const vsk_dp_job *__restrict__ jobs, const uint32_t *__restrict__ order,
@@ -401,18 +421,26 @@ vsk_dp_pass_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
                    const int4 *__restrict__ res, int64_t n, double target, int32_t *__restrict__ nexp,
                    unsigned long long *__restrict__ stats /* [3]=passed [4]=abort */) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int4 r = res[i];
-    const double sim = __dsub_rn(1.0, __ddiv_rn((double)r.y, __dmul_rn(255.0, (double)r.z)));
-    if (jobs[i].br >= 0 && r.w > 5000) atomicAdd(&stats[4], 1ull);  // profile.h:1960-1965 exit(1)
-    int ne = 0;
-    if (sim >= target) {
-        const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
-        const int rq = p >> 1, rr = h >> 1;
-        ne = (refs.rot_off[rr + 1] - refs.rot_off[rr]) * (reads.rot_off[rq + 1] - reads.rot_off[rq]);
-        atomicAdd(&stats[3], 1ull);
+    unsigned passed = 0, aborts = 0;
+    if (i < n) {
+        const int4 r = res[i];
+        const double sim = __dsub_rn(1.0, __ddiv_rn((double)r.y, __dmul_rn(255.0, (double)r.z)));
+        if (jobs[i].br >= 0 && r.w > 5000) aborts = 1;  // profile.h:1960-1965 exit(1)
+        int ne = 0;
+        if (sim >= target) {
+            const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
+            const int rq = p >> 1, rr = h >> 1;
+            ne = (refs.rot_off[rr + 1] - refs.rot_off[rr]) * (reads.rot_off[rq + 1] - reads.rot_off[rq]);
+            passed = 1;
+        }
+        nexp[i] = ne;
     }
-    nexp[i] = ne;
+    passed = __reduce_add_sync(0xffffffffu, passed);
+    aborts = __reduce_add_sync(0xffffffffu, aborts);
+    if ((threadIdx.x & 31) == 0) {
+        if (passed) atomicAdd(&stats[3], (unsigned long long)passed);
+        if (aborts) atomicAdd(&stats[4], (unsigned long long)aborts);
+    }
 }
 
 __global__ void __launch_bounds__(128)
@@ -557,8 +585,8 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, S.get(&res, (size_t)ndp));
     const int homology_int = (int)((prm->cutoff / 100.0) * 100);  // TARGET_HOMOLOGY_INT, psearch.c:1003
     const double tan_angle = tan(acos(homology_int / 100.0));
-    vsk_dp_jobs_kernel<<<blocks(ndp, 128), 128, 0, st>>>(refs, reads, pairs2, ndp, tan_angle, jobs, cost, unc,
-                                                        d_stats);
+    vsk_dp_jobs_kernel<<<blocks(ndp, 128), 128, 0, st>>>(refs, reads, pairs2, ndp, tan_angle, prm->count_cells, jobs,
+                                                        cost, unc, d_stats);
     vsk_iota_kernel<<<blocks(ndp, 256), 256, 0, st>>>(order, ndp);
     ctx->launches += 2;
     unsigned long long hs[8];
