@@ -84,7 +84,8 @@ extern "C" int vsk_init(vsk_ctx **out, int device, const uint8_t *sm) {
     }
     VSK_CUDA(ctx, cudaMalloc(&ctx->d_dist, full.size()));
     VSK_CUDA(ctx, cudaMalloc(&ctx->d_gapnd, gapnd.size() * sizeof(uint16_t)));
-    VSK_CUDA(ctx, cudaMalloc(&ctx->d_queue, 64));
+    VSK_CUDA(ctx, cudaMalloc(&ctx->d_queue, 256));
+    ctx->h_dist = full;
     VSK_CUDA(ctx, cudaMemcpy(ctx->d_dist, full.data(), full.size(), cudaMemcpyHostToDevice));
     VSK_CUDA(ctx, cudaMemcpy(ctx->d_gapnd, gapnd.data(), gapnd.size() * sizeof(uint16_t),
                              cudaMemcpyHostToDevice));
@@ -99,6 +100,8 @@ extern "C" void vsk_destroy(vsk_ctx *ctx) {
     cudaFree(ctx->d_gapnd);
     cudaFree(ctx->d_queue);
     cudaFree(ctx->d_dp_scratch);
+    cudaFree(ctx->d_tiny_dense);
+    cudaFree(ctx->d_tiny_ktab);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -140,6 +143,8 @@ extern "C" int vsk_profset_upload(vsk_ctx *ctx, int32_t n, const int64_t *off, c
         VSK_CUDA(ctx, cudaMemcpyAsync(ps->d_ids, ids + off[0], sizeof(uint16_t) * (size_t)total,
                                       cudaMemcpyHostToDevice, ctx->stream));
     VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    memset(&ps->present, 0, sizeof ps->present);
+    for (int64_t i = 0; i < total; ++i) ps->present.bits[ids[off[0] + i] >> 5] |= 1u << (ids[off[0] + i] & 31);
     *out = ps;
     return VSK_OK;
 }
@@ -154,9 +159,10 @@ extern "C" void vsk_profset_free(vsk_ctx *ctx, vsk_profset *ps) {
 
 // ---- pair DP -----------------------------------------------------------------
 struct vsk_dp_batch {
-    int64_t n = 0;
+    int64_t n = 0, n_tiny = 0;
     int64_t cells = 0;
     int32_t max_l1 = 0;
+    vsk_idset ids;
     const vsk_profset *left = nullptr, *top = nullptr;
     vsk_dp_job *d_jobs = nullptr;
     int4 *d_out = nullptr;
@@ -198,8 +204,9 @@ extern "C" int vsk_dp_batch_prepare(vsk_ctx *ctx, const vsk_profset *L, const vs
         } else {
             cells += (int64_t)j.l1 * j.l2;
         }
-        // kernel cost ~ strips * (rows + pipeline fill)
-        cost[(size_t)i] = (int64_t)((j.l2 + 255) / 256) * (j.l1 + 31);
+        // warp-per-pair jobs first (cost ~ strips * (rows + pipeline fill), heaviest first), tiny jobs last
+        if (VSK_DP_TINY(j.l1, j.l2, j.br)) cost[(size_t)i] = j.l1 * 64 + j.l2;
+        else cost[(size_t)i] = ((int64_t)1 << 32) + (int64_t)((j.l2 + 255) / 256) * (j.l1 + 31);
         max_l1 = std::max(max_l1, j.l1);
     }
     std::vector<int64_t> order((size_t)n);
@@ -210,6 +217,9 @@ extern "C" int vsk_dp_batch_prepare(vsk_ctx *ctx, const vsk_profset *L, const vs
     for (int64_t i = 0; i < n; ++i) sorted[(size_t)i] = jobs[(size_t)order[(size_t)i]];
     vsk_dp_batch *b = new vsk_dp_batch();
     b->n = n;
+    for (int64_t i = 0; i < n; ++i)
+        if (VSK_DP_TINY(jobs[(size_t)i].l1, jobs[(size_t)i].l2, jobs[(size_t)i].br)) b->n_tiny++;
+    for (int k = 0; k < 32; ++k) b->ids.bits[k] = L->present.bits[k] | T->present.bits[k];
     b->cells = cells;
     b->max_l1 = max_l1;
     b->left = L;
@@ -227,7 +237,7 @@ extern "C" int vsk_dp_batch_prepare(vsk_ctx *ctx, const vsk_profset *L, const vs
 
 extern "C" int vsk_dp_batch_run(vsk_ctx *ctx, vsk_dp_batch *b) {
     if (!ctx || !b) return VSK_ERR_ARG;
-    return vsk_dp_launch(ctx, b->left->d_ids, b->top->d_ids, b->d_jobs, b->n, b->max_l1, b->d_out);
+    return vsk_dp_launch(ctx, b->left->d_ids, b->top->d_ids, b->d_jobs, b->n, b->n_tiny, b->max_l1, &b->ids, b->d_out);
 }
 
 extern "C" int vsk_dp_batch_fetch(vsk_ctx *ctx, vsk_dp_batch *b, vsk_dp_result *out) {

@@ -22,6 +22,8 @@
 // row*svector, profile.h:1835-1839) is applied as a mask: out-of-band cells are
 // VSK_BIG, exactly the value of the sentinels the reference plants beside the
 // band (profile.h:1850-1877), so they never win or tie against in-band cells.
+#include <algorithm>
+
 #include "vsk_internal.cuh"
 
 #define DP_WARPS 4
@@ -322,50 +324,228 @@ vsk_dp_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict_
     }
 }
 
+// ---- thread-per-pair kernel for tiny pairs ---------------------------------------------
+// Most pairs PROCLU aligns are tiny (patterns of 7-30 columns): on the warp-per-pair kernel they
+// pay 31 pipeline-fill steps and a per-pair table build for a few hundred cells.  Here one thread
+// owns one pair (full matrix only, <= 32 columns, <= 64 rows): its previous row lives in shared
+// memory laid out [column][thread] (conflict free), the cell state is packed in two words
+// (w0 = distance:15 | length:7 | sumw:10 -- the bounds follow from the size limits -- and
+// w1 = dsum), and substitution costs come from a dense K x K table over the composition ids that
+// actually occur in the two profile sets, resident in shared memory.
+#define TINY_THREADS 128
+#define TINY_MAXCOLS 32
+#define TINY_MAXROWS 64
+#define TINY_DMASK 0x7fffu
+#define TINY_LEN1 (1u << 15)
+#define TINY_W1 (1u << 22)
+
+__global__ void __launch_bounds__(TINY_THREADS)
+vsk_dp_tiny_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
+                   const vsk_dp_job *__restrict__ jobs, int n_jobs, const uint8_t *__restrict__ dense,
+                   const uint8_t *__restrict__ ktab, int K, const uint16_t *__restrict__ gapnd,
+                   int4 *__restrict__ out) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint32_t *s_w0 = reinterpret_cast<uint32_t *>(smem);                 // [33][128]
+    uint32_t *s_w1 = s_w0 + (TINY_MAXCOLS + 1) * TINY_THREADS;           // [33][128]
+    uint32_t *s_col = s_w1 + (TINY_MAXCOLS + 1) * TINY_THREADS;          // [32][128]
+    uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(s_col + TINY_MAXCOLS * TINY_THREADS);  // [1024]
+    uint8_t *s_dense = reinterpret_cast<uint8_t *>(s_gapnd + 1024);      // [1024]
+    uint8_t *s_ktab = s_dense + 1024;                                    // [K*K]
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 1024; i += TINY_THREADS) { s_gapnd[i] = gapnd[i]; s_dense[i] = dense[i]; }
+    for (int i = tid; i < K * K; i += TINY_THREADS) s_ktab[i] = ktab[i];
+    __syncthreads();
+    const int ji = blockIdx.x * TINY_THREADS + tid;
+    if (ji >= n_jobs) return;
+    const vsk_dp_job job = jobs[ji];
+    const uint16_t *L = left_ids + job.left_off;
+    const uint16_t *T = top_ids + job.top_off;
+    const int l1 = job.l1, l2 = job.l2;
+    // column constants and row 0 (profile.h:2074-2079)
+    uint32_t w0 = 0, w1 = 0;
+    s_w0[tid] = 0;
+    s_w1[tid] = 0;
+    for (int c = 0; c < l2; ++c) {
+        const int id = T[c];
+        const uint32_t gn = s_gapnd[id];
+        const uint32_t g = gn & 255u, nd = gn >> 8;
+        s_col[c * TINY_THREADS + tid] = (uint32_t)s_dense[id] | (g << 8) | (nd << 16);
+        w0 += g + TINY_LEN1 + nd * TINY_W1;
+        w1 += nd * g;
+        s_w0[(c + 1) * TINY_THREADS + tid] = w0;
+        s_w1[(c + 1) * TINY_THREADS + tid] = w1;
+    }
+    uint32_t lf0 = 0, lf1 = 0;
+    for (int r = 0; r < l1; ++r) {
+        const int id = L[r];
+        const uint32_t gn = s_gapnd[id];
+        const uint32_t gl = gn & 255u, ndl = gn >> 8;
+        const uint8_t *krow = s_ktab + (int)s_dense[id] * K;
+        const uint32_t rinc0 = gl + TINY_LEN1 + ndl * TINY_W1, rinc1 = ndl * gl;
+        // column 0 (profile.h:2084-2090)
+        uint32_t dg0 = s_w0[tid], dg1 = s_w1[tid];
+        lf0 = dg0 + rinc0;
+        lf1 = dg1 + rinc1;
+        s_w0[tid] = lf0;
+        s_w1[tid] = lf1;
+        for (int c = 1; c <= l2; ++c) {
+            const uint32_t cc = s_col[(c - 1) * TINY_THREADS + tid];
+            const uint32_t up0 = s_w0[c * TINY_THREADS + tid], up1 = s_w1[c * TINY_THREADS + tid];
+            const uint32_t gt = (cc >> 8) & 255u, ndt = cc >> 16;
+            const uint32_t dlt = krow[cc & 255u];
+            const uint32_t sa = (dg0 & TINY_DMASK) + dlt;
+            const uint32_t f = (up0 & TINY_DMASK) + gl;
+            const uint32_t e = (lf0 & TINY_DMASK) + gt;
+            // min3switch (profile.h:1098-1099)
+            const bool pF = f <= e;
+            const uint32_t m1 = pF ? f : e;
+            const bool pD = sa <= m1;
+            uint32_t dn = ndl + ndt;
+            dn = dn < 10u ? dn : 10u;
+            uint32_t n0, n1;
+            if (pD) { n0 = dg0 + dlt + TINY_LEN1 + dn * TINY_W1; n1 = dg1 + dn * dlt; }
+            else if (pF) { n0 = up0 + rinc0; n1 = up1 + rinc1; }
+            else { n0 = lf0 + gt + TINY_LEN1 + ndt * TINY_W1; n1 = lf1 + ndt * gt; }
+            dg0 = up0; dg1 = up1;
+            lf0 = n0; lf1 = n1;
+            s_w0[c * TINY_THREADS + tid] = n0;
+            s_w1[c * TINY_THREADS + tid] = n1;
+        }
+    }
+    out[job.out_idx] = make_int4((int)(lf0 & TINY_DMASK), (int)lf1, (int)(lf0 >> 22), (int)((lf0 >> 15) & 127u));
+}
+
+__global__ void vsk_id_presence_kernel(const uint16_t *__restrict__ ids, int64_t n, uint32_t *__restrict__ out) {
+    __shared__ uint32_t bm[32];
+    if (threadIdx.x < 32) bm[threadIdx.x] = 0;
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int id = ids[i];
+        const uint32_t bit = 1u << (id & 31);
+        if (!(bm[id >> 5] & bit)) atomicOr(&bm[id >> 5], bit);
+    }
+    __syncthreads();
+    if (threadIdx.x < 32 && bm[threadIdx.x]) atomicOr(&out[threadIdx.x], bm[threadIdx.x]);
+}
+
+int vsk_id_presence(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out) {
+    memset(out, 0, sizeof *out);
+    if (n <= 0) return VSK_OK;
+    uint32_t *d = reinterpret_cast<uint32_t *>(ctx->d_queue) + 16;  // 32 spare words of the counter block
+    VSK_CUDA(ctx, cudaMemsetAsync(d, 0, sizeof(out->bits), ctx->stream));
+    const int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+    vsk_id_presence_kernel<<<grid, 256, 0, ctx->stream>>>(d_ids, n, d);
+    ctx->launches++;
+    VSK_CUDA(ctx, cudaGetLastError());
+    VSK_CUDA(ctx, cudaMemcpyAsync(out->bits, d, sizeof(out->bits), cudaMemcpyDeviceToHost, ctx->stream));
+    VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VSK_OK;
+}
+
+// dense tables for the id set `ids` (cached in the context); returns K, or 0 when too large
+static int tiny_tables(vsk_ctx *ctx, const vsk_idset *ids, int *K_out) {
+    *K_out = 0;
+    if (!ids) return VSK_OK;
+    if (ctx->tiny_valid && memcmp(&ctx->tiny_key, ids, sizeof *ids) == 0) {
+        *K_out = ctx->tiny_K;
+        return VSK_OK;
+    }
+    std::vector<int> present;
+    for (int id = 0; id < VSK_NIDS; ++id)
+        if (ids->bits[id >> 5] & (1u << (id & 31))) present.push_back(id);
+    const int K = (int)present.size();
+    ctx->tiny_key = *ids;
+    ctx->tiny_valid = true;
+    ctx->tiny_K = 0;
+    if (K == 0 || K > 200) return VSK_OK;  // K*K bytes must fit beside the row buffers in shared memory
+    std::vector<uint8_t> dense(1024, 0), ktab((size_t)K * K);
+    for (int a = 0; a < K; ++a) {
+        dense[(size_t)present[(size_t)a]] = (uint8_t)a;
+        for (int b = 0; b < K; ++b)
+            ktab[(size_t)a * K + b] = ctx->h_dist[(size_t)present[(size_t)a] * VSK_DROW + present[(size_t)b]];
+    }
+    if (!ctx->d_tiny_dense) {
+        VSK_CUDA(ctx, cudaMalloc(&ctx->d_tiny_dense, 1024));
+        VSK_CUDA(ctx, cudaMalloc(&ctx->d_tiny_ktab, 200 * 200));
+    }
+    VSK_CUDA(ctx, cudaMemcpyAsync(ctx->d_tiny_dense, dense.data(), 1024, cudaMemcpyHostToDevice, ctx->stream));
+    VSK_CUDA(ctx, cudaMemcpyAsync(ctx->d_tiny_ktab, ktab.data(), ktab.size(), cudaMemcpyHostToDevice, ctx->stream));
+    VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->tiny_K = K;
+    *K_out = K;
+    return VSK_OK;
+}
+
 static int g_dp_attr_set = 0;
+static int g_tiny_attr_set = 0;
 
 int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids,
-                  const vsk_dp_job *d_jobs, int64_t n_jobs, int32_t max_l1, int4 *d_out) {
+                  const vsk_dp_job *d_jobs, int64_t n_jobs, int64_t n_tiny, int32_t max_l1,
+                  const vsk_idset *ids, int4 *d_out) {
     if (n_jobs <= 0) return VSK_OK;
     if (n_jobs > 0x7fffffff) return vsk_fail(ctx, VSK_ERR_ARG, "too many DP pairs in one launch");
-    if (!g_dp_attr_set) {
-        VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)DP_SMEM_BYTES));
-        g_dp_attr_set = 1;
+    int K = 0;
+    if (n_tiny > 0) {
+        int rc = tiny_tables(ctx, ids, &K);
+        if (rc) return rc;
     }
-    int per_sm = 0;
-    VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_kernel, DP_WARPS * 32,
-                                                                 DP_SMEM_BYTES));
-    if (per_sm < 1) per_sm = 1;
-    int64_t grid = (int64_t)ctx->sm_count * per_sm;  // persistent: one wave, work pulled from a queue
-    const int64_t need = (n_jobs + DP_WARPS - 1) / DP_WARPS;
-    if (grid > need) grid = need;
-    const int stride = ((max_l1 + 31) / 32) * 32;
-    const size_t bytes = (size_t)grid * DP_WARPS * (stride + stride / 4) * sizeof(int4);  // boundary + row records
-    if (bytes > ctx->dp_scratch_bytes) {
-        if (ctx->d_dp_scratch) VSK_CUDA(ctx, cudaFree(ctx->d_dp_scratch));
-        ctx->d_dp_scratch = nullptr;
-        ctx->dp_scratch_bytes = 0;
-        VSK_CUDA(ctx, cudaMalloc(&ctx->d_dp_scratch, bytes));
-        ctx->dp_scratch_bytes = bytes;
-    }
-    VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
+    if (K == 0) n_tiny = 0;
+    const int64_t n_warp = n_jobs - n_tiny;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->profile) {
         VSK_CUDA(ctx, cudaEventCreate(&e0));
         VSK_CUDA(ctx, cudaEventCreate(&e1));
         VSK_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
     }
-    vsk_dp_kernel<<<(unsigned)grid, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
-        d_left_ids, d_top_ids, d_jobs, (int)n_jobs, ctx->d_dist, ctx->d_gapnd,
-        (int4 *)ctx->d_dp_scratch, stride, ctx->d_queue, d_out);
+    if (n_warp > 0) {
+        if (!g_dp_attr_set) {
+            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)DP_SMEM_BYTES));
+            g_dp_attr_set = 1;
+        }
+        int per_sm = 0;
+        VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_kernel, DP_WARPS * 32,
+                                                                     DP_SMEM_BYTES));
+        if (per_sm < 1) per_sm = 1;
+        int64_t grid = (int64_t)ctx->sm_count * per_sm;  // persistent: one wave, work pulled from a queue
+        const int64_t need = (n_warp + DP_WARPS - 1) / DP_WARPS;
+        if (grid > need) grid = need;
+        const int stride = ((max_l1 + 31) / 32) * 32;
+        const size_t bytes = (size_t)grid * DP_WARPS * (stride + stride / 4) * sizeof(int4);  // boundary + row records
+        if (bytes > ctx->dp_scratch_bytes) {
+            if (ctx->d_dp_scratch) VSK_CUDA(ctx, cudaFree(ctx->d_dp_scratch));
+            ctx->d_dp_scratch = nullptr;
+            ctx->dp_scratch_bytes = 0;
+            VSK_CUDA(ctx, cudaMalloc(&ctx->d_dp_scratch, bytes));
+            ctx->dp_scratch_bytes = bytes;
+        }
+        VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
+        vsk_dp_kernel<<<(unsigned)grid, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
+            d_left_ids, d_top_ids, d_jobs, (int)n_warp, ctx->d_dist, ctx->d_gapnd,
+            (int4 *)ctx->d_dp_scratch, stride, ctx->d_queue, d_out);
+        ctx->launches++;
+        VSK_CUDA(ctx, cudaGetLastError());
+    }
+    if (n_tiny > 0) {
+        const size_t smem = (size_t)(2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 + 2048 + 1024 +
+                            (size_t)K * K;
+        if (!g_tiny_attr_set) {
+            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)((2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 +
+                                                     2048 + 1024 + 200 * 200)));
+            g_tiny_attr_set = 1;
+        }
+        vsk_dp_tiny_kernel<<<(unsigned)((n_tiny + TINY_THREADS - 1) / TINY_THREADS), TINY_THREADS, smem, ctx->stream>>>(
+            d_left_ids, d_top_ids, d_jobs + n_warp, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,
+            ctx->d_gapnd, d_out);
+        ctx->launches++;
+        VSK_CUDA(ctx, cudaGetLastError());
+    }
     if (ctx->profile) {
         VSK_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
         ctx->prof_events.push_back(e0);
         ctx->prof_events.push_back(e1);
     }
-    ctx->launches++;
-    VSK_CUDA(ctx, cudaGetLastError());
     return VSK_OK;
 }
 

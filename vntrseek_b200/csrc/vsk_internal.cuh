@@ -16,6 +16,11 @@
 #define VSK_LEN1 (1 << 17)   // path-length unit packed above sumw (sumw <= 10*(L1+L2) < 2^17)
 #define VSK_MAXPROF 6000     // longest profile accepted by the DP kernels
 
+// presence bitmap over composition ids 0..1023
+struct vsk_idset {
+    uint32_t bits[32];
+};
+
 struct vsk_ctx {
     int device = 0;
     int sm_count = 0;
@@ -28,6 +33,13 @@ struct vsk_ctx {
     void *d_dp_scratch = nullptr;
     size_t dp_scratch_bytes = 0;
     int *d_queue = nullptr;       // dynamic work counter
+    std::vector<uint8_t> h_dist;  // host copy of the symmetric table
+    // dense-alphabet tables of the thread-per-pair DP kernel, cached per id set
+    vsk_idset tiny_key;
+    bool tiny_valid = false;
+    int tiny_K = 0;
+    uint8_t *d_tiny_dense = nullptr;  // [1024] composition id -> dense index
+    uint8_t *d_tiny_ktab = nullptr;   // [K*K] distances between present ids
     std::string err;
     uint64_t launches = 0;        // kernels launched through this context
     // optional per-launch timing of the DP kernel (bench.py's roofline leg)
@@ -42,6 +54,7 @@ struct vsk_ctx {
 void vsk_stage_mark(vsk_ctx *ctx, const char *name);
 
 struct vsk_profset {
+    vsk_idset present;
     int32_t n = 0;
     int64_t total = 0;
     int64_t *d_off = nullptr;   // [n+1]
@@ -72,8 +85,15 @@ struct vsk_dp_job {   // one pair as the kernel sees it (sorted by cost, heavies
     double svector;
 };
 
+// Jobs are ordered: the warp-per-pair jobs (heaviest first), then `n_tiny` jobs that satisfy
+// VSK_DP_TINY, which go to the thread-per-pair kernel when `ids` (the composition ids that occur
+// in both profile sets) is given and small enough for the dense table to fit in shared memory.
+#define VSK_DP_TINY(l1, l2, br) ((br) < 0 && (l2) <= 32 && (l1) <= 64)
 int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids,
-                  const vsk_dp_job *d_jobs, int64_t n_jobs, int32_t max_l1, int4 *d_out);
+                  const vsk_dp_job *d_jobs, int64_t n_jobs, int64_t n_tiny, int32_t max_l1,
+                  const vsk_idset *ids, int4 *d_out);
+// which composition ids occur in d_ids[0..n)
+int vsk_id_presence(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out);
 
 int vsk_lcs_launch(vsk_ctx *ctx, const uint8_t *d_seqA, const int64_t *d_offA, const uint8_t *d_seqB,
                    const int64_t *d_offB, const int32_t *d_ia, const int32_t *d_ib, int64_t n,

@@ -55,6 +55,7 @@ struct vsk_reads {
     DevTR d;
     std::vector<void *> allocs;
     int64_t h2d_bytes = 0;
+    vsk_idset present;  // composition ids that occur in this set
 };
 
 struct vsk_refs {
@@ -104,7 +105,7 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
 #undef UP
     VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     *out = r;
-    return VSK_OK;
+    return vsk_id_presence(ctx, r->d.ids, (int64_t)ts->ids.size(), &r->present);
 }
 
 static void free_reads(vsk_reads *r) {
@@ -340,7 +341,7 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
                    unsigned long long *__restrict__ stats /* [0]=cells [1]=n_uncertain [2]=max_l1 [6]=id+result bytes */) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long cells = 0, bytes = 0;
-    unsigned nunc = 0;
+    unsigned nunc = 0, ntiny = 0;
     int maxl1 = 0;
     if (i < n) {
         const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
@@ -382,7 +383,10 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
             }
         }
         jobs[i] = j;
-        cost[i] = (uint32_t)(((j.l2 + 255) >> 8) * (j.l1 + 31));
+        // warp-per-pair jobs sort before the tiny (thread-per-pair) ones, each group heaviest first
+        const bool tiny = VSK_DP_TINY(j.l1, j.l2, j.br);
+        cost[i] = tiny ? (uint32_t)(j.l1 * 64 + j.l2) : ((1u << 20) + (uint32_t)(((j.l2 + 255) >> 8) * (j.l1 + 31)));
+        ntiny = tiny ? 1u : 0u;
         uncertain[i] = unc;
         nunc = unc;
         maxl1 = j.l1;
@@ -394,6 +398,7 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
         cells += __shfl_down_sync(0xffffffffu, cells, o);
         bytes += __shfl_down_sync(0xffffffffu, bytes, o);
         nunc += __shfl_down_sync(0xffffffffu, nunc, o);
+        ntiny += __shfl_down_sync(0xffffffffu, ntiny, o);
         maxl1 = max(maxl1, __shfl_down_sync(0xffffffffu, maxl1, o));
     }
     if ((threadIdx.x & 31) == 0) {
@@ -401,6 +406,7 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
         if (nunc) atomicAdd(&stats[1], (unsigned long long)nunc);
         atomicMax(&stats[2], (unsigned long long)maxl1);
         atomicAdd(&stats[6], bytes);
+        if (ntiny) atomicAdd(&stats[7], (unsigned long long)ntiny);
     }
 }
 
@@ -621,13 +627,15 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     }
     out->stats.dp_alg_bytes += (int64_t)hs[6];
     size_t tb4 = 0;
-    cub::DeviceRadixSort::SortPairsDescending(nullptr, tb4, cost, cost2, order, order2, ndp, 0, 20, st);
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, tb4, cost, cost2, order, order2, ndp, 0, 21, st);
     if (tb4 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb4)); tb = tb4; }
-    VSK_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, tb, cost, cost2, order, order2, ndp, 0, 20, st));
+    VSK_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, tb, cost, cost2, order, order2, ndp, 0, 21, st));
     vsk_gather_jobs_kernel<<<blocks(ndp, 256), 256, 0, st>>>(jobs, order2, ndp, sorted);
     ctx->launches++;
     vsk_stage_mark(ctx, "dp_schedule");
-    int rc = vsk_dp_launch(ctx, refs.ids, reads.ids, sorted, ndp, (int32_t)hs[2], res);
+    vsk_idset ids;
+    for (int k = 0; k < 32; ++k) ids.bits[k] = R->tr->present.bits[k] | Q->present.bits[k];
+    int rc = vsk_dp_launch(ctx, refs.ids, reads.ids, sorted, ndp, (int64_t)hs[7], (int32_t)hs[2], &ids, res);
     if (rc) return rc;
     vsk_stage_mark(ctx, "dp_kernel");
     // similarity test + flank expansion
