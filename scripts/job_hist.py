@@ -21,4 +21,6 @@ edges = [0, 16, 32, 64, 128, 256, 512, 1024, 2048, 8192]
 for a, b in zip(edges[:-1], edges[1:]):
     m = (l2 > a) & (l2 <= b)
     print(f"l2 in ({a},{b}]: pairs {m.mean()*100:6.2f}%  cells {cells[m].sum()/cells.sum()*100:6.2f}%  mean l1 {l1[m].mean() if m.any() else 0:.0f}")
-np.save("gpurun_out/jobs_sample.npy", j[:: max(1, len(j) // 200000)])
+os.makedirs("gpurun_out", exist_ok=True)
+np.save("gpurun_out/jobs_sample.npy", j[:: max(1, len(j) // 400000)])
+print("TOTALJOBS", len(j))

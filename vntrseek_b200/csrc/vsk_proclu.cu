@@ -32,6 +32,11 @@ struct DevTR {
     int32_t *leftlen = nullptr, *rightlen = nullptr, *patlen = nullptr, *key = nullptr;
     int32_t *rot_off = nullptr, *rot_mem = nullptr;
     uint8_t *dir = nullptr, *master = nullptr;
+    // consensus in bit-parallel form, 64 characters per block (built on the device after upload):
+    // cons_planes[4*b + c] = bit i set iff character i of block b is "ACGT"[c];
+    // cons_codes[2*b + k]  = 2-bit codes of characters 32k..32k+31 of block b
+    int64_t *cons_blk = nullptr;  // [2n+1] first block of every profile's consensus
+    uint64_t *cons_planes = nullptr, *cons_codes = nullptr;
 };
 
 struct DevIndex {
@@ -84,6 +89,39 @@ static int upload_vec(vsk_ctx *ctx, std::vector<void *> &allocs, const std::vect
     return VSK_OK;
 }
 
+__device__ __forceinline__ int base_code(uint8_t c) {
+    return (c == 'C') ? 1 : (c == 'G') ? 2 : (c == 'T') ? 3 : 0;
+}
+
+// one warp per profile: consensus ASCII -> match planes + 2-bit codes, 64 characters per block
+__global__ void __launch_bounds__(256) vsk_pack_consensus_kernel(DevTR t, int64_t nprof) {
+    const int64_t p = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (p >= nprof) return;
+    const uint8_t *seq = t.cons + t.cons_off[p];
+    const int len = (int)(t.cons_off[p + 1] - t.cons_off[p]);
+    const int64_t b0 = t.cons_blk[p];
+    const int nblk = (len + 63) >> 6;
+    for (int b = 0; b < nblk; ++b) {
+        uint32_t pl[2][4];
+        uint64_t code[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int i = b * 64 + h * 32 + lane;
+            const int c = (i < len) ? base_code(seq[i]) : -1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) pl[h][k] = __ballot_sync(0xffffffffu, c == k);
+            // 2-bit codes: lane l contributes bits 2l, 2l+1
+            const uint32_t lo = __ballot_sync(0xffffffffu, c >= 0 && (c & 1)), hi = __ballot_sync(0xffffffffu, c >= 0 && (c & 2));
+            uint64_t w = 0;
+            for (int l = 0; l < 32; ++l) w |= ((uint64_t)((lo >> l) & 1u) | ((uint64_t)((hi >> l) & 1u) << 1)) << (2 * l);
+            code[h] = w;
+        }
+        if (lane < 4) t.cons_planes[4 * (b0 + b) + lane] = (uint64_t)pl[0][lane] | ((uint64_t)pl[1][lane] << 32);
+        if (lane < 2) t.cons_codes[2 * (b0 + b) + lane] = code[lane];
+    }
+}
+
 static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
     vsk_reads *r = new vsk_reads();
     r->ctx = ctx;
@@ -103,6 +141,22 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
     UP(cons, cons) UP(fl, fl) UP(leftlen, ts->leftlen) UP(rightlen, ts->rightlen) UP(patlen, ts->patlen)
     UP(key, ts->key) UP(rot_off, rot_off) UP(rot_mem, rot_mem) UP(dir, ts->dir) UP(master, ts->master)
 #undef UP
+    {
+        const size_t np = (size_t)2 * ts->n;
+        std::vector<int64_t> blk(np + 1, 0);
+        for (size_t p = 0; p < np; ++p) blk[p + 1] = blk[p] + (ts->cons_off[p + 1] - ts->cons_off[p] + 63) / 64;
+        const int64_t nblk = blk[np];
+        if ((rc = upload_vec(ctx, r->allocs, blk, &r->d.cons_blk, &r->h2d_bytes))) { *out = r; return rc; }
+        VSK_CUDA(ctx, cudaMalloc((void **)&r->d.cons_planes, sizeof(uint64_t) * 4 * (size_t)(nblk + 1)));
+        r->allocs.push_back(r->d.cons_planes);
+        VSK_CUDA(ctx, cudaMalloc((void **)&r->d.cons_codes, sizeof(uint64_t) * 2 * (size_t)(nblk + 1)));
+        r->allocs.push_back(r->d.cons_codes);
+        if (np) {
+            vsk_pack_consensus_kernel<<<(unsigned)((np * 32 + 255) / 256), 256, 0, ctx->stream>>>(r->d, (int64_t)np);
+            ctx->launches++;
+            VSK_CUDA(ctx, cudaGetLastError());
+        }
+    }
     VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     *out = r;
     return vsk_id_presence(ctx, r->d.ids, (int64_t)ts->ids.size(), &r->present);
@@ -209,9 +263,6 @@ extern "C" void vsk_refs_free(vsk_ctx *ctx, vsk_refs *R) {
 extern "C" int64_t vsk_refs_seed_hits(const vsk_refs *R) { return R ? R->total_hits : 0; }
 
 // ---------------------------------------------------------------- kernels
-__device__ __forceinline__ int base_code(uint8_t c) {
-    return (c == 'C') ? 1 : (c == 'G') ? 2 : (c == 'T') ? 3 : 0;
-}
 
 // window of one seed code inside the index: distinct entries [s,e2) plus, when an
 // entry past `hi` exists, the head hit of that next pattern-size group (hclust.h:380-421)
@@ -320,6 +371,16 @@ vsk_seed_kernel(DevTR reads, DevIndex idx, DevLuts luts, int32_t p_begin, int32_
     }
 }
 
+// LCS filter on the packed consensus strings.  Same result as LCS_multiple_word /
+// LCS_single_word on the ASCII strings (the consensus holds only A,C,G,T): any exact bit-vector
+// LCS gives the same length, so the vectors here index character i at bit i of block i/64; the
+// single-word copy's 0x10 bitmask quirk (single word.c:59) is the truncation of the longer string
+// to 60 characters when its length is 61..63.
+__device__ __forceinline__ uint64_t lcs_plane(const uint64_t (&pl)[4], uint32_t code) {
+    const uint64_t lo = (code & 1u) ? pl[1] : pl[0], hi = (code & 1u) ? pl[3] : pl[2];
+    return (code & 2u) ? hi : lo;
+}
+
 __global__ void __launch_bounds__(128)
 vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__restrict__ pairs, int64_t n,
                       uint8_t *__restrict__ flags) {
@@ -328,9 +389,58 @@ vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__r
     const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
     const int nr = (int)(refs.cons_off[h + 1] - refs.cons_off[h]);
     const int mr = (int)(reads.cons_off[p + 1] - reads.cons_off[p]);
-    const int lcs = vsk_lcs_device(refs.cons + refs.cons_off[h], nr, reads.cons + reads.cons_off[p], mr);
-    const int shortest = min(nr, mr);
-    flags[i] = (lcs >= luts.lcs_min[shortest]) ? 1 : 0;  // hclust.h:537-545
+    // the longer string is bit-indexed; on a tie string1 = the reference (multiple word.c:76-86)
+    const bool ref_is_text = nr >= mr;
+    const uint64_t *planes = ref_is_text ? refs.cons_planes + 4 * refs.cons_blk[h] : reads.cons_planes + 4 * reads.cons_blk[p];
+    const uint64_t *codes = ref_is_text ? reads.cons_codes + 2 * reads.cons_blk[p] : refs.cons_codes + 2 * refs.cons_blk[h];
+    int N = ref_is_text ? nr : mr;
+    const int M = ref_is_text ? mr : nr;
+    const int shortest = M;
+    if (N <= 63 && N > 60) N = 60;
+    int count = 0;
+    if (N <= 64) {  // one block: no carries between words
+        uint64_t pl[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) pl[k] = planes[k];
+        const uint64_t valid = (N == 64) ? ~0ull : ((1ull << N) - 1ull);
+        uint64_t V = ~0ull, cw = 0;
+        for (int r = 0; r < M; ++r) {
+            if ((r & 31) == 0) cw = codes[r >> 5];
+            const uint64_t m = lcs_plane(pl, (uint32_t)(cw >> (2 * (r & 31))) & 3u) & valid;
+            const uint64_t x = V & m;
+            V = (V + x) | (V & ~m);
+        }
+        count = __popcll(~V & valid);
+    } else {
+        const int W = (N + 63) >> 6;
+        uint64_t carry[VSK_CW];
+        for (int j = 0; j < W; ++j) {
+            uint64_t pl[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) pl[k] = planes[4 * j + k];
+            const int top = N - j * 64;  // valid characters in this block
+            const uint64_t valid = (top >= 64) ? ~0ull : ((1ull << top) - 1ull);
+            uint64_t V = ~0ull, cw = 0, cin_w = 0, cout_w = 0;
+            for (int r = 0; r < M; ++r) {
+                if ((r & 31) == 0) cw = codes[r >> 5];
+                if ((r & 63) == 0) {
+                    if (j > 0) cin_w = carry[r >> 6];
+                    cout_w = 0;
+                }
+                const uint64_t m = lcs_plane(pl, (uint32_t)(cw >> (2 * (r & 31))) & 3u) & valid;
+                const uint64_t x = V & m;
+                const uint64_t s1 = V + x;
+                uint64_t co = (s1 < x) ? 1ull : 0ull;
+                const uint64_t s2 = s1 + ((cin_w >> (r & 63)) & 1ull);
+                co |= (s2 < s1) ? 1ull : 0ull;
+                V = s2 | (V & ~m);
+                cout_w |= co << (r & 63);
+                if ((r & 63) == 63 || r == M - 1) carry[r >> 6] = cout_w;
+            }
+            count += __popcll(~V & valid);
+        }
+    }
+    flags[i] = (count >= luts.lcs_min[shortest]) ? 1 : 0;  // hclust.h:537-545
 }
 
 // DP job per surviving pair (hclust.h:550-577) + its scheduling key
