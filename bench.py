@@ -261,6 +261,7 @@ def ours(args, rank, world, local_rank):
     t = time.perf_counter()
     refs_ts = v.TRSetHandle.from_packed(refs, is_read=False)
     reads_ts = v.TRSetHandle.from_packed(reads, is_read=True, maxflank=50)
+    reads_ts.pin()  # e2e leg copies the step's inputs from pinned host memory
     pack_s = time.perf_counter() - t
     t = time.perf_counter()
     idx = v.RefIndex(ctx, refs_ts)

@@ -170,6 +170,8 @@ int vsk_trset_from_arrays(int32_t n, const int32_t *key, const int32_t *patlen,
 int vsk_trset_apply_rotindex(vsk_trset *ts, const char *path);
 /* psearch.c:397-401,424-428: a key may appear once across both files */
 int vsk_trsets_check_unique(const vsk_trset *a, const vsk_trset *b, int32_t *dup_key);
+/* page-lock the set's large arrays (one-time) so vsk_proclu_run's H2D copies run at PCIe rate */
+int vsk_trset_pin(vsk_trset *ts);
 int32_t vsk_trset_size(const vsk_trset *ts);
 const char *vsk_trset_error(const vsk_trset *ts);
 void vsk_trset_free(vsk_trset *ts);

@@ -90,6 +90,7 @@ def _declare2(L):
                                         C.POINTER(vp)]
     L.vsk_trset_apply_rotindex.argtypes = [vp, C.c_char_p]
     L.vsk_trsets_check_unique.argtypes = [vp, vp, C.POINTER(C.c_int32)]
+    L.vsk_trset_pin.argtypes = [vp]
     L.vsk_trset_size.argtypes = [vp]
     L.vsk_trset_size.restype = C.c_int32
     L.vsk_trset_error.argtypes = [vp]

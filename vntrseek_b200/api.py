@@ -223,6 +223,12 @@ class TRSetHandle:
         if rc != 0:
             raise VskError(lib().vsk_trset_error(self.h).decode())
 
+    def pin(self):
+        """page-lock the host arrays (vsk_trset_pin)"""
+        if lib().vsk_trset_pin(self.h) != 0:
+            raise VskError("vsk_trset_pin failed")
+        return self
+
     def __len__(self):
         return lib().vsk_trset_size(self.h)
 

@@ -159,7 +159,7 @@ extern "C" void vsk_profset_free(vsk_ctx *ctx, vsk_profset *ps) {
 
 // ---- pair DP -----------------------------------------------------------------
 struct vsk_dp_batch {
-    int64_t n = 0, n_tiny = 0;
+    int64_t n = 0, n_tiny = 0, n_q8 = 0;
     int64_t cells = 0;
     int32_t max_l1 = 0;
     vsk_idset ids;
@@ -205,8 +205,7 @@ extern "C" int vsk_dp_batch_prepare(vsk_ctx *ctx, const vsk_profset *L, const vs
             cells += (int64_t)j.l1 * j.l2;
         }
         // warp-per-pair jobs first (cost ~ strips * (rows + pipeline fill), heaviest first), tiny jobs last
-        if (VSK_DP_TINY(j.l1, j.l2, j.br)) cost[(size_t)i] = j.l1 * 64 + j.l2;
-        else cost[(size_t)i] = ((int64_t)1 << 32) + (int64_t)((j.l2 + 255) / 256) * (j.l1 + 31);
+        cost[(size_t)i] = (int64_t)vsk_dp_sort_key(j.l1, j.l2, j.br);
         max_l1 = std::max(max_l1, j.l1);
     }
     std::vector<int64_t> order((size_t)n);
@@ -218,7 +217,10 @@ extern "C" int vsk_dp_batch_prepare(vsk_ctx *ctx, const vsk_profset *L, const vs
     vsk_dp_batch *b = new vsk_dp_batch();
     b->n = n;
     for (int64_t i = 0; i < n; ++i)
+    {
         if (VSK_DP_TINY(jobs[(size_t)i].l1, jobs[(size_t)i].l2, jobs[(size_t)i].br)) b->n_tiny++;
+        else if (VSK_DP_Q8(jobs[(size_t)i].l1, jobs[(size_t)i].l2, jobs[(size_t)i].br)) b->n_q8++;
+    }
     for (int k = 0; k < 32; ++k) b->ids.bits[k] = L->present.bits[k] | T->present.bits[k];
     b->cells = cells;
     b->max_l1 = max_l1;
@@ -237,7 +239,7 @@ extern "C" int vsk_dp_batch_prepare(vsk_ctx *ctx, const vsk_profset *L, const vs
 
 extern "C" int vsk_dp_batch_run(vsk_ctx *ctx, vsk_dp_batch *b) {
     if (!ctx || !b) return VSK_ERR_ARG;
-    return vsk_dp_launch(ctx, b->left->d_ids, b->top->d_ids, b->d_jobs, b->n, b->n_tiny, b->max_l1, &b->ids, b->d_out);
+    return vsk_dp_launch(ctx, b->left->d_ids, b->top->d_ids, b->d_jobs, b->n, b->n_q8, b->n_tiny, b->max_l1, &b->ids, b->d_out);
 }
 
 extern "C" int vsk_dp_batch_fetch(vsk_ctx *ctx, vsk_dp_batch *b, vsk_dp_result *out) {

@@ -324,6 +324,134 @@ vsk_dp_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict_
     }
 }
 
+// ---- quarter-warp kernel for medium pairs ------------------------------------------------
+// Pairs with at most 128 columns waste most of a warp's pipeline (31 fill steps, a per-pair
+// table build).  Here 8 lanes own a pair (four pairs per warp, each group with its own job
+// loop and its own sync mask), one strip of 8*CPL columns, and the substitution costs come from
+// the dense K x K table of the data set in shared memory, so there is no per-pair set-up.
+#define Q8_WARPS 4
+#define Q8_G 8
+
+template <int CPL>
+__device__ __forceinline__ void dp_q8_pair(const vsk_dp_job &job, const uint16_t *__restrict__ L,
+                                           const uint16_t *__restrict__ Tp, const uint16_t *s_gapnd,
+                                           const uint8_t *s_dense, const uint8_t *s_ktab, int K,
+                                           unsigned gmask, int glane, int4 *out) {
+    const int l1 = job.l1, l2 = job.l2, br = job.br;
+    const bool banded = br >= 0;
+    const double sv = job.svector;
+    const int cbase = glane * CPL;
+    int Hd[CPL], Hp1[CPL], Hp2[CPL], tb[CPL], gt[CPL], ci1[CPL], ci2[CPL];
+    int sd = 0, s1 = 0, s2 = 0;
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+        const int c = cbase + j;
+        const int id = (c < l2) ? (int)Tp[c] : 0;
+        const int gn = s_gapnd[id];
+        const int g = gn & 255, nd = gn >> 8;
+        gt[j] = g;
+        ci1[j] = nd * g;
+        ci2[j] = nd + VSK_LEN1;
+        tb[j] = s_dense[id];
+        sd += g; s1 += nd * g; s2 += nd + VSK_LEN1;
+        Hd[j] = sd; Hp1[j] = s1; Hp2[j] = s2;
+    }
+    int xd = sd, x1 = s1, x2 = s2;
+#pragma unroll
+    for (int o = 1; o < Q8_G; o <<= 1) {
+        const int a = __shfl_up_sync(gmask, xd, o, Q8_G);
+        const int b = __shfl_up_sync(gmask, x1, o, Q8_G);
+        const int c = __shfl_up_sync(gmask, x2, o, Q8_G);
+        if (glane >= o) { xd += a; x1 += b; x2 += c; }
+    }
+    const int ed = xd - sd, e1 = x1 - s1, e2 = x2 - s2;
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+        Hd[j] += ed; Hp1[j] += e1; Hp2[j] += e2;
+        if (banded && cbase + j + 1 > br) Hd[j] = VSK_BIG;
+    }
+    int dgd = ed, dgp1 = e1, dgp2 = e2;
+    if (banded && cbase > br) dgd = VSK_BIG;
+    int id_next = L[min(max(-glane, 0), l1 - 1)];
+
+    auto step = [&](const int s, const bool check) {
+        const int r = s - glane;
+        int lfd = __shfl_up_sync(gmask, Hd[CPL - 1], 1, Q8_G);
+        int lfp1 = __shfl_up_sync(gmask, Hp1[CPL - 1], 1, Q8_G);
+        int lfp2 = __shfl_up_sync(gmask, Hp2[CPL - 1], 1, Q8_G);
+        const bool active = !check || ((r >= 0) && (r < l1));
+        const int id = id_next;
+        id_next = L[min(max(r + 1, 0), l1 - 1)];
+        const int gn = s_gapnd[id];
+        const int gl = gn & 255, ndl = gn >> 8;
+        const int ri1 = ndl * gl, ri2 = ndl + VSK_LEN1;
+        const uint8_t *trow = s_ktab + (int)s_dense[id] * K;
+        int lo = 0, hi = CPL;
+        bool need_mask = false;
+        if (active) {
+            if (glane == 0) { lfd = dgd + gl; lfp1 = dgp1 + ri1; lfp2 = dgp2 + ri2; }
+            if (banded) {  // profile.h:1835-1839
+                const int center = __double2int_rz(__dmul_rn((double)(r + 1), sv));
+                lo = max(1, center - br) - (cbase + 1);
+                hi = min(l2, center + br) - (cbase + 1);
+                need_mask = (lo > 0) || (hi < CPL - 1);
+            }
+        }
+        const bool anymask = banded && (__ballot_sync(gmask, need_mask) != 0u);
+        if (active) {
+            if (anymask)
+                dp_row_cells<CPL, true, true>(Hd, Hp1, Hp2, tb, gt, ci1, ci2, dgd, dgp1, dgp2, lfd, lfp1, lfp2, trow,
+                                              gl, ndl, ri1, ri2, lo, hi);
+            else
+                dp_row_cells<CPL, false, true>(Hd, Hp1, Hp2, tb, gt, ci1, ci2, dgd, dgp1, dgp2, lfd, lfp1, lfp2, trow,
+                                               gl, ndl, ri1, ri2, lo, hi);
+            dgd = lfd; dgp1 = lfp1; dgp2 = lfp2;
+        }
+    };
+    const int s_fill_end = min(Q8_G - 1, l1 + Q8_G - 1);
+    int s = 0;
+    for (; s < s_fill_end; ++s) step(s, true);
+    for (; s < l1; ++s) step(s, false);
+    for (; s < l1 + Q8_G - 1; ++s) step(s, true);
+    const int cl = l2 - 1;
+    if (glane == cl / CPL) {
+        const int jr = cl % CPL;
+#pragma unroll
+        for (int j = 0; j < CPL; ++j)
+            if (j == jr)
+                out[job.out_idx] = make_int4(Hd[j], Hp1[j], Hp2[j] & (VSK_LEN1 - 1), Hp2[j] >> 17);
+    }
+}
+
+__global__ void __launch_bounds__(Q8_WARPS * 32)
+vsk_dp_q8_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
+                 const vsk_dp_job *__restrict__ jobs, int n_jobs, const uint8_t *__restrict__ dense,
+                 const uint8_t *__restrict__ ktab, int K, const uint16_t *__restrict__ gapnd, int *queue,
+                 int4 *__restrict__ out) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(smem);
+    uint8_t *s_dense = smem + 2048;
+    uint8_t *s_ktab = s_dense + 1024;
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) { s_gapnd[i] = gapnd[i]; s_dense[i] = dense[i]; }
+    for (int i = threadIdx.x; i < K * K; i += blockDim.x) s_ktab[i] = ktab[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, glane = lane & (Q8_G - 1);
+    const unsigned gmask = 0xffu << (lane & ~(Q8_G - 1));
+    for (;;) {
+        int ji = 0;
+        if (glane == 0) ji = atomicAdd(queue, 1);
+        ji = __shfl_sync(gmask, ji, 0, Q8_G);
+        if (ji >= n_jobs) break;
+        const vsk_dp_job job = jobs[ji];
+        const uint16_t *L = left_ids + job.left_off;
+        const uint16_t *Tp = top_ids + job.top_off;
+        if (job.l2 <= 32) dp_q8_pair<4>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, gmask, glane, out);
+        else if (job.l2 <= 64) dp_q8_pair<8>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, gmask, glane, out);
+        else dp_q8_pair<16>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, gmask, glane, out);
+        __syncwarp(gmask);
+    }
+}
+
 // ---- thread-per-pair kernel for tiny pairs ---------------------------------------------
 // Most pairs PROCLU aligns are tiny (patterns of 7-30 columns): on the warp-per-pair kernel they
 // pay 31 pipeline-fill steps and a per-pair table build for a few hundred cells.  Here one thread
@@ -479,18 +607,20 @@ static int tiny_tables(vsk_ctx *ctx, const vsk_idset *ids, int *K_out) {
 static int g_dp_attr_set = 0;
 static int g_tiny_attr_set = 0;
 
+static int g_q8_attr_set = 0;
+
 int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids,
-                  const vsk_dp_job *d_jobs, int64_t n_jobs, int64_t n_tiny, int32_t max_l1,
+                  const vsk_dp_job *d_jobs, int64_t n_jobs, int64_t n_q8, int64_t n_tiny, int32_t max_l1,
                   const vsk_idset *ids, int4 *d_out) {
     if (n_jobs <= 0) return VSK_OK;
     if (n_jobs > 0x7fffffff) return vsk_fail(ctx, VSK_ERR_ARG, "too many DP pairs in one launch");
     int K = 0;
-    if (n_tiny > 0) {
+    if (n_tiny > 0 || n_q8 > 0) {
         int rc = tiny_tables(ctx, ids, &K);
         if (rc) return rc;
     }
-    if (K == 0) n_tiny = 0;
-    const int64_t n_warp = n_jobs - n_tiny;
+    if (K == 0) n_tiny = n_q8 = 0;  // no dense table: everything goes through the warp-per-pair kernel
+    const int64_t n_warp = n_jobs - n_tiny - n_q8;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->profile) {
         VSK_CUDA(ctx, cudaEventCreate(&e0));
@@ -526,6 +656,26 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         ctx->launches++;
         VSK_CUDA(ctx, cudaGetLastError());
     }
+    if (n_q8 > 0) {
+        const size_t smem = 2048 + 1024 + (size_t)K * K;
+        if (!g_q8_attr_set) {
+            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_q8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               2048 + 1024 + 200 * 200));
+            g_q8_attr_set = 1;
+        }
+        int per_sm = 0;
+        VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_q8_kernel, Q8_WARPS * 32, smem));
+        if (per_sm < 1) per_sm = 1;
+        int64_t grid = (int64_t)ctx->sm_count * per_sm;
+        const int64_t need = (n_q8 + Q8_WARPS * 4 - 1) / (Q8_WARPS * 4);
+        if (grid > need) grid = need;
+        VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue + 1, 0, sizeof(int), ctx->stream));
+        vsk_dp_q8_kernel<<<(unsigned)grid, Q8_WARPS * 32, smem, ctx->stream>>>(
+            d_left_ids, d_top_ids, d_jobs + n_warp, (int)n_q8, ctx->d_tiny_dense, ctx->d_tiny_ktab, K, ctx->d_gapnd,
+            ctx->d_queue + 1, d_out);
+        ctx->launches++;
+        VSK_CUDA(ctx, cudaGetLastError());
+    }
     if (n_tiny > 0) {
         const size_t smem = (size_t)(2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 + 2048 + 1024 +
                             (size_t)K * K;
@@ -536,7 +686,7 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
             g_tiny_attr_set = 1;
         }
         vsk_dp_tiny_kernel<<<(unsigned)((n_tiny + TINY_THREADS - 1) / TINY_THREADS), TINY_THREADS, smem, ctx->stream>>>(
-            d_left_ids, d_top_ids, d_jobs + n_warp, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,
+            d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,
             ctx->d_gapnd, d_out);
         ctx->launches++;
         VSK_CUDA(ctx, cudaGetLastError());

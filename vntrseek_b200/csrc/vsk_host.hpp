@@ -31,6 +31,10 @@ struct vsk_trset {
     std::vector<std::vector<int32_t>> rotlist; // [n] member record indices, self first
     std::unordered_map<int32_t, int32_t> by_key;
     std::string err;
+    // rotlists flattened for the device (built on demand, dropped when the lists change)
+    std::vector<int32_t> rot_off, rot_mem;
+    bool rot_flat = false;
+    std::vector<void *> pinned;  // host ranges registered with cudaHostRegister (vsk_trset_pin)
 };
 
 // Seed geometry per TRANGE (psearch.c:161-318)

@@ -89,8 +89,16 @@ struct vsk_dp_job {   // one pair as the kernel sees it (sorted by cost, heavies
 // VSK_DP_TINY, which go to the thread-per-pair kernel when `ids` (the composition ids that occur
 // in both profile sets) is given and small enough for the dense table to fit in shared memory.
 #define VSK_DP_TINY(l1, l2, br) ((br) < 0 && (l2) <= 32 && (l1) <= 64)
+// ... preceded by `n_q8` jobs for the quarter-warp kernel: at most 128 columns and not tiny
+#define VSK_DP_Q8(l1, l2, br) ((l2) <= 128 && !VSK_DP_TINY(l1, l2, br))
+// scheduling key (sorted descending): class, then size
+__host__ __device__ inline uint32_t vsk_dp_sort_key(int l1, int l2, int br) {
+    if (VSK_DP_TINY(l1, l2, br)) return (uint32_t)(l1 * 64 + l2);
+    if (VSK_DP_Q8(l1, l2, br)) return (1u << 20) | ((uint32_t)((l2 > 64) ? 2 : (l2 > 32) ? 1 : 0) << 14) | (uint32_t)min(l1, 16383);
+    return (2u << 20) + (uint32_t)(((l2 + 255) >> 8) * (l1 + 31));
+}
 int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids,
-                  const vsk_dp_job *d_jobs, int64_t n_jobs, int64_t n_tiny, int32_t max_l1,
+                  const vsk_dp_job *d_jobs, int64_t n_jobs, int64_t n_q8, int64_t n_tiny, int32_t max_l1,
                   const vsk_idset *ids, int4 *d_out);
 // which composition ids occur in d_ids[0..n)
 int vsk_id_presence(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out);

@@ -259,6 +259,7 @@ extern "C" int vsk_trset_apply_rotindex(vsk_trset *ts, const char *path) {
             } else {
                 const int32_t m = it->second;
                 ts->rotlist[master].push_back(m);
+                ts->rot_flat = false;
                 ts->master[m] = 0;
                 ts->dir[m] = (uint8_t)(firstdir ? !d : d);
             }
@@ -268,7 +269,34 @@ extern "C" int vsk_trset_apply_rotindex(vsk_trset *ts, const char *path) {
     return VSK_OK;
 }
 
-extern "C" void vsk_trset_free(vsk_trset *ts) { delete ts; }
+// Page-lock the large arrays of a TR set so that vsk_proclu_run's host->device copies run at
+// full PCIe rate (one-time cost; undone by vsk_trset_free).
+extern "C" int vsk_trset_pin(vsk_trset *ts) {
+    if (!ts) return VSK_ERR_ARG;
+    if (!ts->pinned.empty()) return VSK_OK;
+    auto pin = [&](void *p, size_t bytes) {
+        if (bytes < (1u << 16)) return;
+        if (cudaHostRegister(p, bytes, cudaHostRegisterPortable) == cudaSuccess) ts->pinned.push_back(p);
+        else cudaGetLastError();
+    };
+    pin(ts->ids.data(), ts->ids.size() * sizeof(uint16_t));
+    pin(ts->cons.data(), ts->cons.size());
+    pin(ts->fl.data(), ts->fl.size());
+    pin(ts->prof_off.data(), ts->prof_off.size() * sizeof(int64_t));
+    pin(ts->cons_off.data(), ts->cons_off.size() * sizeof(int64_t));
+    pin(ts->fl_off.data(), ts->fl_off.size() * sizeof(int64_t));
+    pin(ts->leftlen.data(), ts->leftlen.size() * sizeof(int32_t));
+    pin(ts->rightlen.data(), ts->rightlen.size() * sizeof(int32_t));
+    pin(ts->patlen.data(), ts->patlen.size() * sizeof(int32_t));
+    pin(ts->key.data(), ts->key.size() * sizeof(int32_t));
+    return VSK_OK;
+}
+
+extern "C" void vsk_trset_free(vsk_trset *ts) {
+    if (!ts) return;
+    for (void *p : ts->pinned) cudaHostUnregister(p);
+    delete ts;
+}
 extern "C" int32_t vsk_trset_size(const vsk_trset *ts) { return ts ? ts->n : 0; }
 extern "C" const char *vsk_trset_error(const vsk_trset *ts) { return ts ? ts->err.c_str() : ""; }
 

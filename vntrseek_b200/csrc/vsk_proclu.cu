@@ -81,7 +81,7 @@ __constant__ int c_nones[15];
 template <typename T>
 static int upload_vec(vsk_ctx *ctx, std::vector<void *> &allocs, const std::vector<T> &h, T **d,
                       int64_t *bytes = nullptr, size_t pad = 8) {
-    VSK_CUDA(ctx, cudaMalloc((void **)d, sizeof(T) * (h.size() + pad)));
+    VSK_CUDA(ctx, cudaMallocAsync((void **)d, sizeof(T) * (h.size() + pad), ctx->stream));
     allocs.push_back(*d);
     if (!h.empty())
         VSK_CUDA(ctx, cudaMemcpyAsync(*d, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, ctx->stream));
@@ -122,34 +122,54 @@ __global__ void __launch_bounds__(256) vsk_pack_consensus_kernel(DevTR t, int64_
     }
 }
 
+static int upload_raw(vsk_ctx *ctx, std::vector<void *> &allocs, const uint8_t *h, size_t n, uint8_t **d,
+                      int64_t *bytes) {
+    VSK_CUDA(ctx, cudaMallocAsync((void **)d, n + 64, ctx->stream));
+    allocs.push_back(*d);
+    if (n) VSK_CUDA(ctx, cudaMemcpyAsync(*d, h, n, cudaMemcpyHostToDevice, ctx->stream));
+    if (bytes) *bytes += (int64_t)n;
+    return VSK_OK;
+}
+
+static void keep_pool(vsk_ctx *ctx);
+
 static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
+    keep_pool(ctx);
     vsk_reads *r = new vsk_reads();
     r->ctx = ctx;
     r->host = ts;
     r->d.n = ts->n;
     int rc;
-    std::vector<uint8_t> cons(ts->cons.begin(), ts->cons.end()), fl(ts->fl.begin(), ts->fl.end());
-    std::vector<int32_t> rot_off((size_t)ts->n + 1, 0), rot_mem;
-    for (int32_t i = 0; i < ts->n; ++i) {
-        rot_off[(size_t)i] = (int32_t)rot_mem.size();
-        rot_mem.insert(rot_mem.end(), ts->rotlist[(size_t)i].begin(), ts->rotlist[(size_t)i].end());
+    if (!ts->rot_flat) {  // flatten the rotlists once (cache inside the TR set)
+        vsk_trset *mt = const_cast<vsk_trset *>(ts);
+        mt->rot_off.assign((size_t)ts->n + 1, 0);
+        mt->rot_mem.clear();
+        for (int32_t i = 0; i < ts->n; ++i) {
+            mt->rot_off[(size_t)i] = (int32_t)mt->rot_mem.size();
+            mt->rot_mem.insert(mt->rot_mem.end(), ts->rotlist[(size_t)i].begin(), ts->rotlist[(size_t)i].end());
+        }
+        mt->rot_off[(size_t)ts->n] = (int32_t)mt->rot_mem.size();
+        mt->rot_flat = true;
     }
-    rot_off[(size_t)ts->n] = (int32_t)rot_mem.size();
 #define UP(field, vec) \
     if ((rc = upload_vec(ctx, r->allocs, vec, &r->d.field, &r->h2d_bytes))) { *out = r; return rc; }
+#define UPB(field, vec)                                                                                   \
+    if ((rc = upload_raw(ctx, r->allocs, reinterpret_cast<const uint8_t *>((vec).data()), (vec).size(),    \
+                         &r->d.field, &r->h2d_bytes))) { *out = r; return rc; }
     UP(prof_off, ts->prof_off) UP(cons_off, ts->cons_off) UP(fl_off, ts->fl_off) UP(ids, ts->ids)
-    UP(cons, cons) UP(fl, fl) UP(leftlen, ts->leftlen) UP(rightlen, ts->rightlen) UP(patlen, ts->patlen)
-    UP(key, ts->key) UP(rot_off, rot_off) UP(rot_mem, rot_mem) UP(dir, ts->dir) UP(master, ts->master)
+    UPB(cons, ts->cons) UPB(fl, ts->fl) UP(leftlen, ts->leftlen) UP(rightlen, ts->rightlen) UP(patlen, ts->patlen)
+    UP(key, ts->key) UP(rot_off, ts->rot_off) UP(rot_mem, ts->rot_mem) UP(dir, ts->dir) UP(master, ts->master)
 #undef UP
+#undef UPB
     {
         const size_t np = (size_t)2 * ts->n;
         std::vector<int64_t> blk(np + 1, 0);
         for (size_t p = 0; p < np; ++p) blk[p + 1] = blk[p] + (ts->cons_off[p + 1] - ts->cons_off[p] + 63) / 64;
         const int64_t nblk = blk[np];
         if ((rc = upload_vec(ctx, r->allocs, blk, &r->d.cons_blk, &r->h2d_bytes))) { *out = r; return rc; }
-        VSK_CUDA(ctx, cudaMalloc((void **)&r->d.cons_planes, sizeof(uint64_t) * 4 * (size_t)(nblk + 1)));
+        VSK_CUDA(ctx, cudaMallocAsync((void **)&r->d.cons_planes, sizeof(uint64_t) * 4 * (size_t)(nblk + 1), ctx->stream));
         r->allocs.push_back(r->d.cons_planes);
-        VSK_CUDA(ctx, cudaMalloc((void **)&r->d.cons_codes, sizeof(uint64_t) * 2 * (size_t)(nblk + 1)));
+        VSK_CUDA(ctx, cudaMallocAsync((void **)&r->d.cons_codes, sizeof(uint64_t) * 2 * (size_t)(nblk + 1), ctx->stream));
         r->allocs.push_back(r->d.cons_codes);
         if (np) {
             vsk_pack_consensus_kernel<<<(unsigned)((np * 32 + 255) / 256), 256, 0, ctx->stream>>>(r->d, (int64_t)np);
@@ -164,7 +184,7 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
 
 static void free_reads(vsk_reads *r) {
     if (!r) return;
-    for (void *p : r->allocs) cudaFree(p);
+    for (void *p : r->allocs) cudaFreeAsync(p, r->ctx->stream);
     delete r;
 }
 
@@ -256,7 +276,8 @@ extern "C" void vsk_refs_free(vsk_ctx *ctx, vsk_refs *R) {
     if (!R) return;
     if (ctx) cudaSetDevice(ctx->device);
     free_reads(R->tr);
-    for (void *p : R->allocs) cudaFree(p);
+    for (void *p : R->allocs) cudaFreeAsync(p, R->ctx->stream);
+    cudaStreamSynchronize(R->ctx->stream);
     delete R;
 }
 
@@ -383,64 +404,116 @@ __device__ __forceinline__ uint64_t lcs_plane(const uint64_t (&pl)[4], uint32_t 
 
 __global__ void __launch_bounds__(128)
 vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__restrict__ pairs, int64_t n,
-                      uint8_t *__restrict__ flags) {
+                      uint8_t *__restrict__ flags, uint32_t *__restrict__ long_list, unsigned *__restrict__ long_count) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t p = (uint32_t)(pairs[i] >> 32), h = (uint32_t)pairs[i];
-    const int nr = (int)(refs.cons_off[h + 1] - refs.cons_off[h]);
-    const int mr = (int)(reads.cons_off[p + 1] - reads.cons_off[p]);
+    const bool in_range = i < n;
+    const uint64_t key = in_range ? pairs[i] : 0ull;
+    const uint32_t p = (uint32_t)(key >> 32), h = (uint32_t)key;
+    const int nr = in_range ? (int)(refs.cons_off[h + 1] - refs.cons_off[h]) : 0;
+    const int mr = in_range ? (int)(reads.cons_off[p + 1] - reads.cons_off[p]) : 0;
     // the longer string is bit-indexed; on a tie string1 = the reference (multiple word.c:76-86)
     const bool ref_is_text = nr >= mr;
-    const uint64_t *planes = ref_is_text ? refs.cons_planes + 4 * refs.cons_blk[h] : reads.cons_planes + 4 * reads.cons_blk[p];
-    const uint64_t *codes = ref_is_text ? reads.cons_codes + 2 * reads.cons_blk[p] : refs.cons_codes + 2 * refs.cons_blk[h];
     int N = ref_is_text ? nr : mr;
     const int M = ref_is_text ? mr : nr;
     const int shortest = M;
     if (N <= 63 && N > 60) N = 60;
-    int count = 0;
-    if (N <= 64) {  // one block: no carries between words
-        uint64_t pl[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) pl[k] = planes[k];
-        const uint64_t valid = (N == 64) ? ~0ull : ((1ull << N) - 1ull);
-        uint64_t V = ~0ull, cw = 0;
-        for (int r = 0; r < M; ++r) {
-            if ((r & 31) == 0) cw = codes[r >> 5];
-            const uint64_t m = lcs_plane(pl, (uint32_t)(cw >> (2 * (r & 31))) & 3u) & valid;
-            const uint64_t x = V & m;
-            V = (V + x) | (V & ~m);
-        }
-        count = __popcll(~V & valid);
-    } else {
-        const int W = (N + 63) >> 6;
-        uint64_t carry[VSK_CW];
-        for (int j = 0; j < W; ++j) {
-            uint64_t pl[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) pl[k] = planes[4 * j + k];
-            const int top = N - j * 64;  // valid characters in this block
-            const uint64_t valid = (top >= 64) ? ~0ull : ((1ull << top) - 1ull);
-            uint64_t V = ~0ull, cw = 0, cin_w = 0, cout_w = 0;
-            for (int r = 0; r < M; ++r) {
-                if ((r & 31) == 0) cw = codes[r >> 5];
-                if ((r & 63) == 0) {
-                    if (j > 0) cin_w = carry[r >> 6];
-                    cout_w = 0;
-                }
-                const uint64_t m = lcs_plane(pl, (uint32_t)(cw >> (2 * (r & 31))) & 3u) & valid;
-                const uint64_t x = V & m;
-                const uint64_t s1 = V + x;
-                uint64_t co = (s1 < x) ? 1ull : 0ull;
-                const uint64_t s2 = s1 + ((cin_w >> (r & 63)) & 1ull);
-                co |= (s2 < s1) ? 1ull : 0ull;
-                V = s2 | (V & ~m);
-                cout_w |= co << (r & 63);
-                if ((r & 63) == 63 || r == M - 1) carry[r >> 6] = cout_w;
-            }
-            count += __popcll(~V & valid);
+    // more than one block: left to vsk_lcs_long_kernel (work queue), which keeps this kernel's warps
+    // uniform; one counter update per warp
+    const bool is_long = in_range && N > 64;
+    const unsigned lmask = __ballot_sync(0xffffffffu, is_long);
+    if (lmask) {
+        const int lane = threadIdx.x & 31, leader = __ffs(lmask) - 1;
+        unsigned base = 0;
+        if (lane == leader) base = atomicAdd(long_count, (unsigned)__popc(lmask));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (is_long) {
+            long_list[base + __popc(lmask & ((1u << lane) - 1u))] = (uint32_t)i;
+            flags[i] = 0;
         }
     }
+    if (!in_range || is_long) return;
+    const uint64_t *planes = ref_is_text ? refs.cons_planes + 4 * refs.cons_blk[h] : reads.cons_planes + 4 * reads.cons_blk[p];
+    const uint64_t *codes = ref_is_text ? reads.cons_codes + 2 * reads.cons_blk[p] : refs.cons_codes + 2 * refs.cons_blk[h];
+    uint64_t pl[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) pl[k] = planes[k];
+    const uint64_t valid = (N == 64) ? ~0ull : ((1ull << N) - 1ull);
+    uint64_t V = ~0ull, cw = 0;
+    for (int r = 0; r < M; ++r) {
+        if ((r & 31) == 0) cw = codes[r >> 5];
+        const uint64_t m = lcs_plane(pl, (uint32_t)(cw >> (2 * (r & 31))) & 3u) & valid;
+        const uint64_t x = V & m;
+        V = (V + x) | (V & ~m);
+    }
+    const int count = __popcll(~V & valid);
     flags[i] = (count >= luts.lcs_min[shortest]) ? 1 : 0;  // hclust.h:537-545
+}
+
+// The multi-block pairs deferred by vsk_lcs_filter_kernel.  Persistent threads; every lane pulls
+// its own next pair from a counter and the loop body is exactly one (block, row) step of the
+// recurrence, so lanes that are working on different pairs still execute the same instructions.
+// Word-outer / row-inner order with the inter-word carries kept one bit per row (as vsk_bits.cuh).
+__global__ void __launch_bounds__(128)
+vsk_lcs_long_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__restrict__ pairs,
+                    const uint32_t *__restrict__ long_list, const unsigned *__restrict__ long_count,
+                    unsigned *__restrict__ head, uint8_t *__restrict__ flags) {
+    const unsigned n = *long_count;
+    uint64_t carry[VSK_CW];
+    const uint64_t *planes = nullptr, *codes = nullptr;
+    uint64_t pl[4] = {0, 0, 0, 0}, V = 0, valid = 0, cw = 0, cin_w = 0, cout_w = 0;
+    int N = 0, M = 0, W = 0, j = 0, r = 0, count = 0, shortest = 0;
+    uint32_t item = 0;
+    bool have = false;
+    for (;;) {
+        if (!have) {
+            const unsigned k = atomicAdd(head, 1u);
+            if (k >= n) break;
+            item = long_list[k];
+            const uint32_t p = (uint32_t)(pairs[item] >> 32), h = (uint32_t)pairs[item];
+            const int nr = (int)(refs.cons_off[h + 1] - refs.cons_off[h]);
+            const int mr = (int)(reads.cons_off[p + 1] - reads.cons_off[p]);
+            const bool ref_is_text = nr >= mr;
+            planes = ref_is_text ? refs.cons_planes + 4 * refs.cons_blk[h] : reads.cons_planes + 4 * reads.cons_blk[p];
+            codes = ref_is_text ? reads.cons_codes + 2 * reads.cons_blk[p] : refs.cons_codes + 2 * refs.cons_blk[h];
+            N = ref_is_text ? nr : mr;
+            M = ref_is_text ? mr : nr;
+            shortest = M;
+            W = (N + 63) >> 6;
+            j = 0;
+            r = 0;
+            count = 0;
+            have = true;
+        }
+        if (r == 0) {  // start of a block
+#pragma unroll
+            for (int k = 0; k < 4; ++k) pl[k] = planes[4 * j + k];
+            const int top = N - j * 64;
+            valid = (top >= 64) ? ~0ull : ((1ull << top) - 1ull);
+            V = ~0ull;
+        }
+        if ((r & 31) == 0) cw = codes[r >> 5];
+        if ((r & 63) == 0) {
+            cin_w = (j > 0) ? carry[r >> 6] : 0ull;
+            cout_w = 0;
+        }
+        const uint64_t m = lcs_plane(pl, (uint32_t)(cw >> (2 * (r & 31))) & 3u) & valid;
+        const uint64_t x = V & m;
+        const uint64_t s1 = V + x;
+        uint64_t co = (s1 < x) ? 1ull : 0ull;
+        const uint64_t s2 = s1 + ((cin_w >> (r & 63)) & 1ull);
+        co |= (s2 < s1) ? 1ull : 0ull;
+        V = s2 | (V & ~m);
+        cout_w |= co << (r & 63);
+        if ((r & 63) == 63 || r == M - 1) carry[r >> 6] = cout_w;
+        if (++r == M) {
+            count += __popcll(~V & valid);
+            r = 0;
+            if (++j == W) {
+                flags[item] = (count >= luts.lcs_min[shortest]) ? 1 : 0;
+                have = false;
+            }
+        }
+    }
 }
 
 // DP job per surviving pair (hclust.h:550-577) + its scheduling key
@@ -494,9 +567,9 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
         }
         jobs[i] = j;
         // warp-per-pair jobs sort before the tiny (thread-per-pair) ones, each group heaviest first
-        const bool tiny = VSK_DP_TINY(j.l1, j.l2, j.br);
-        cost[i] = tiny ? (uint32_t)(j.l1 * 64 + j.l2) : ((1u << 20) + (uint32_t)(((j.l2 + 255) >> 8) * (j.l1 + 31)));
-        ntiny = tiny ? 1u : 0u;
+        cost[i] = vsk_dp_sort_key(j.l1, j.l2, j.br);
+        // low half: tiny (thread-per-pair) jobs, high half: quarter-warp jobs
+        ntiny = VSK_DP_TINY(j.l1, j.l2, j.br) ? 1u : (VSK_DP_Q8(j.l1, j.l2, j.br) ? 0x10000u : 0u);
         uncertain[i] = unc;
         nunc = unc;
         maxl1 = j.l1;
@@ -516,7 +589,8 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
         if (nunc) atomicAdd(&stats[1], (unsigned long long)nunc);
         atomicMax(&stats[2], (unsigned long long)maxl1);
         atomicAdd(&stats[6], bytes);
-        if (ntiny) atomicAdd(&stats[7], (unsigned long long)ntiny);
+        if (ntiny & 0xffffu) atomicAdd(&stats[7], (unsigned long long)(ntiny & 0xffffu));
+        if (ntiny >> 16) atomicAdd(&stats[8], (unsigned long long)(ntiny >> 16));
     }
 }
 
@@ -631,6 +705,17 @@ struct vsk_proclu_result {
 
 static int g_pool_set = 0;
 
+// keep freed stream-ordered memory in the pool between runs
+static void keep_pool(vsk_ctx *ctx) {
+    if (g_pool_set) return;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) {
+        uint64_t thr = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    g_pool_set = 1;
+}
+
 static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const vsk_proclu_params *prm,
                      int32_t p_begin, int32_t p_end, const int64_t *d_off_emit, int64_t base, int64_t nkeys,
                      vsk_proclu_result *out) {
@@ -644,8 +729,8 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, S.get(&keys, (size_t)nkeys));
     VSK_CUDA(ctx, S.get(&keys2, (size_t)nkeys));
     VSK_CUDA(ctx, S.get(&d_n, 4));
-    VSK_CUDA(ctx, S.get(&d_stats, 8));
-    VSK_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 8 * sizeof(unsigned long long), st));
+    VSK_CUDA(ctx, S.get(&d_stats, 12));
+    VSK_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 12 * sizeof(unsigned long long), st));
     const int64_t nprof = p_end - p_begin;
     vsk_stage_mark(ctx, nullptr);
     vsk_seed_kernel<true><<<blocks(nprof * 32, 256), 256, 0, st>>>(reads, R->idx, R->luts, p_begin, p_end,
@@ -673,8 +758,16 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     // LCS filter
     uint8_t *flags;
     VSK_CUDA(ctx, S.get(&flags, (size_t)npairs));
-    vsk_lcs_filter_kernel<<<blocks(npairs, 128), 128, 0, st>>>(refs, reads, R->luts, pairs, npairs, flags);
-    ctx->launches++;
+    uint32_t *long_list;
+    unsigned *long_ctr;
+    VSK_CUDA(ctx, S.get(&long_list, (size_t)npairs));
+    VSK_CUDA(ctx, S.get(&long_ctr, 2));
+    VSK_CUDA(ctx, cudaMemsetAsync(long_ctr, 0, 2 * sizeof(unsigned), st));
+    vsk_lcs_filter_kernel<<<blocks(npairs, 128), 128, 0, st>>>(refs, reads, R->luts, pairs, npairs, flags, long_list,
+                                                              long_ctr);
+    vsk_lcs_long_kernel<<<(unsigned)ctx->sm_count * 8, 128, 0, st>>>(refs, reads, R->luts, pairs, long_list, long_ctr,
+                                                                    long_ctr + 1, flags);
+    ctx->launches += 2;
     pairs2 = keys2;
     size_t tb3 = 0;
     cub::DeviceSelect::Flagged(nullptr, tb3, pairs, flags, pairs2, d_n, npairs, st);
@@ -705,7 +798,7 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
                                                         cost, unc, d_stats);
     vsk_iota_kernel<<<blocks(ndp, 256), 256, 0, st>>>(order, ndp);
     ctx->launches += 2;
-    unsigned long long hs[8];
+    unsigned long long hs[12];
     VSK_CUDA(ctx, cudaMemcpyAsync(hs, d_stats, sizeof hs, cudaMemcpyDeviceToHost, st));
     VSK_CUDA(ctx, cudaStreamSynchronize(st));
     if (hs[1]) {  // settle band radii the device could not decide
@@ -737,15 +830,15 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     }
     out->stats.dp_alg_bytes += (int64_t)hs[6];
     size_t tb4 = 0;
-    cub::DeviceRadixSort::SortPairsDescending(nullptr, tb4, cost, cost2, order, order2, ndp, 0, 21, st);
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, tb4, cost, cost2, order, order2, ndp, 0, 22, st);
     if (tb4 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb4)); tb = tb4; }
-    VSK_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, tb, cost, cost2, order, order2, ndp, 0, 21, st));
+    VSK_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, tb, cost, cost2, order, order2, ndp, 0, 22, st));
     vsk_gather_jobs_kernel<<<blocks(ndp, 256), 256, 0, st>>>(jobs, order2, ndp, sorted);
     ctx->launches++;
     vsk_stage_mark(ctx, "dp_schedule");
     vsk_idset ids;
     for (int k = 0; k < 32; ++k) ids.bits[k] = R->tr->present.bits[k] | Q->present.bits[k];
-    int rc = vsk_dp_launch(ctx, refs.ids, reads.ids, sorted, ndp, (int64_t)hs[7], (int32_t)hs[2], &ids, res);
+    int rc = vsk_dp_launch(ctx, refs.ids, reads.ids, sorted, ndp, (int64_t)hs[8], (int64_t)hs[7], (int32_t)hs[2], &ids, res);
     if (rc) return rc;
     vsk_stage_mark(ctx, "dp_kernel");
     // similarity test + flank expansion
@@ -803,14 +896,7 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
     *out = nullptr;
     if (prm->option_r) return vsk_fail(ctx, VSK_ERR_ARG, "-r (ref-to-ref) mode is not supported by the GPU path yet");
     VSK_CUDA(ctx, cudaSetDevice(ctx->device));
-    if (!g_pool_set) {  // keep freed stream-ordered memory in the pool between runs
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) {
-            uint64_t thr = ~0ull;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
-        }
-        g_pool_set = 1;
-    }
+    keep_pool(ctx);
     const vsk_trset *hq = Q->host;
     const vsk_seedinfo &si = vsk_seeds();
     for (int32_t q = 0; q < hq->n; ++q) {  // the reference quits on these (psearch.c:784-787, hclust.h:866-869)
