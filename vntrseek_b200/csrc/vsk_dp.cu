@@ -387,19 +387,16 @@ __device__ __forceinline__ void dp_q8_pair(const vsk_dp_job &job, const uint16_t
         const int ri1 = ndl * gl, ri2 = ndl + VSK_LEN1;
         const uint8_t *trow = s_ktab + (int)s_dense[id] * K;
         int lo = 0, hi = CPL;
-        bool need_mask = false;
         if (active) {
             if (glane == 0) { lfd = dgd + gl; lfp1 = dgp1 + ri1; lfp2 = dgp2 + ri2; }
             if (banded) {  // profile.h:1835-1839
                 const int center = __double2int_rz(__dmul_rn((double)(r + 1), sv));
                 lo = max(1, center - br) - (cbase + 1);
                 hi = min(l2, center + br) - (cbase + 1);
-                need_mask = (lo > 0) || (hi < CPL - 1);
             }
-        }
-        const bool anymask = banded && (__ballot_sync(gmask, need_mask) != 0u);
-        if (active) {
-            if (anymask)
+            // the four groups of a warp run different pairs: choosing the masked code per step would
+            // make them diverge, so a banded pair always takes it
+            if (banded)
                 dp_row_cells<CPL, true, true>(Hd, Hp1, Hp2, tb, gt, ci1, ci2, dgd, dgp1, dgp2, lfd, lfp1, lfp2, trow,
                                               gl, ndl, ri1, ri2, lo, hi);
             else
