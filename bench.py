@@ -276,20 +276,11 @@ def ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
         ctx.sync()
 
+    from vntrseek_b200.dist import allgather_links
+
     def merge_links(links):
-        """per-rank link tables -> every rank (NCCL all-gather over NVLink)"""
-        if world == 1:
-            return links
-        n = torch.tensor([len(links)], device="cuda", dtype=torch.int64)
-        ns = [torch.zeros_like(n) for _ in range(world)]
-        dist.all_gather(ns, n)
-        mx = int(max(x.item() for x in ns))
-        buf = torch.zeros((mx, 7), dtype=torch.int32, device="cuda")
-        if len(links):
-            buf[:len(links)] = torch.from_numpy(links.view(np.int32).reshape(-1, 7)).cuda()
-        out = torch.empty((world * mx, 7), dtype=torch.int32, device="cuda")
-        dist.all_gather_into_tensor(out, buf)
-        return out
+        """per-rank link tables -> every rank (one NCCL all-gather over NVLink)"""
+        return allgather_links(links, device="cuda") if world > 1 else links
 
     # ---- device-resident leg ------------------------------------------------
     # untimed pass with exact cell accounting (the same batch is scanned every step)
