@@ -191,7 +191,7 @@ int64_t vsk_refs_seed_hits(const vsk_refs *refs);
 typedef struct {
     int32_t cutoff;      /* argv CUTOFF 70..100 (psearch.c:909-912)                  */
     int32_t maxerrors;   /* argv MAXERRORS, 0 = from flank length (hclust.h:660-668)  */
-    int32_t option_r;    /* -r: not yet on the GPU path (rejected)                   */
+    int32_t option_r;    /* -r: ref-to-ref flank rules (hclust.h:700-751); needs maxerrors 0 */
     int32_t count_cells; /* 1: stats.dp_cells counts the reference's band cells exactly (slower) */
     int64_t key_budget;  /* candidate keys per chunk, 0 = default                    */
 } vsk_proclu_params;
@@ -233,6 +233,9 @@ void vsk_proclu_result_free(vsk_proclu_result *r);
  * (hclust.h:818-822).  *trcount = CLUSTERBASE.trcount ("total clustered").      */
 int vsk_clusters_write(const vsk_link *links, int64_t n, const char *clu_path, const char *map_path,
                        uint64_t *trcount);
+/* -r flavour: leftcon/rightcon marks (hclust.h:825-847) and `key+` / `key-` members (cluster.h:515-522) */
+int vsk_clusters_write_r(const vsk_link *links, int64_t n, const char *clu_path, const char *map_path,
+                         uint64_t *trcount);
 
 /* ---- flankalign ---------------------------------------------------------------------
  * vsk_flankalign_run = the whole of flankalign.exe after argv (reference

@@ -80,3 +80,34 @@ def test_cli_errors_match_reference(tmp_path, dst_file):
     assert run(exe, ["a", "b", dst_file, 50, 0, 50], str(tmp_path))[0] == 1   # cutoff outside 70..100
     assert run(exe, ["a", "b", dst_file, 88, 0, 50, "-m"], str(tmp_path))[0] == 1  # -m at argv[7] is taken as edges file
     assert run(exe, ["nofile", "nofile", dst_file, 88, 0, 50], str(tmp_path))[0] == 1
+
+
+def _canonical_clu_r(path):
+    """-r mode: members carry + / - (a property of the key, not a relative direction)"""
+    out = []
+    for line in open(path):
+        toks = line.split()
+        assert toks[0] == "@"
+        out.append(tuple(sorted((int(t[:-1]), t[-1]) for t in toks[1:])))
+    return sorted(out)
+
+
+@pytest.mark.parametrize("reflen", [50, 20])
+def test_psearch_ref_to_ref_mode(tmp_path, dst_file, reflen):
+    """`-r LEN -m` (produce_indist.pl:156-160): REFLEN flank cut, both flank orders, leftcon/rightcon
+    marks, +/- cluster members, and the map file (compared as a sorted multiset of lines)."""
+    if not _have_ref():
+        pytest.skip("oracle/_ref/psearch.exe not built")
+    a, b = str(tmp_path / "ref"), str(tmp_path / "our")
+    os.makedirs(a)
+    _make(a, 600, 900, 21, 300)
+    shutil.copytree(a, b)
+    args = ["reference.leb36", "reads.leb36", dst_file, 88, 0, 50, "-r", reflen, "-m"]
+    rc1, _, log1 = run(os.path.join(REF_BIN, "psearch.exe"), args, a)
+    rc2, _, log2 = run(os.path.join(OUR_BIN, "psearch.exe"), args, b)
+    assert rc1 == 0 and rc2 == 0, (rc1, rc2, log2[-500:])
+    assert parse_counters(log2) == parse_counters(log1)
+    assert _canonical_clu_r(os.path.join(b, "reads.leb36.clu")) == _canonical_clu_r(os.path.join(a, "reads.leb36.clu"))
+    m1 = sorted(open(os.path.join(a, "reads.leb36.map")).read().splitlines())
+    m2 = sorted(open(os.path.join(b, "reads.leb36.map")).read().splitlines())
+    assert len(m1) > 50 and m1 == m2

@@ -112,7 +112,6 @@ int main(int argc, char **argv) {
         fprintf(stdout, "\nAlignment complete\n");
         exit(0);
     }
-    if (option_r) die("-r (ref-to-ref) mode is not available in the GPU build yet");
 
     fprintf(stderr, "\nReading reference profiles...");
     if (vsk_trset_load_leb36(argv[1], 0, maxflank, option_r, reflen, &refs) != VSK_OK)
@@ -155,7 +154,8 @@ int main(int argc, char **argv) {
         if (vsk_proclu_run(ctx, R, reads, &prm, &res) != VSK_OK) die(vsk_last_error(ctx));
         vsk_proclu_result_stats(res, &st);
         nl = vsk_proclu_result_links(res, &links);
-        rc = vsk_clusters_write(links, nl, NULL, NULL, &trcount);
+        rc = option_r ? vsk_clusters_write_r(links, nl, NULL, NULL, &trcount)
+                      : vsk_clusters_write(links, nl, NULL, NULL, &trcount);
         fprintf(stderr,
                 "\nscan finished!\n\t"
                 "CandidatesConsidered: %llu\n\t"
@@ -171,7 +171,8 @@ int main(int argc, char **argv) {
                 (unsigned long long) st.confirmed, (unsigned long long) trcount,
                 (double) (time(NULL) - startTime));
         fflush(stderr);
-        rc = vsk_clusters_write(links, nl, outputfile, option_m ? mapfile : NULL, &trcount);
+        rc = option_r ? vsk_clusters_write_r(links, nl, outputfile, option_m ? mapfile : NULL, &trcount)
+                      : vsk_clusters_write(links, nl, outputfile, option_m ? mapfile : NULL, &trcount);
         if (rc != VSK_OK) {
             fprintf(stderr, "\nERROR: Unable to create output file '%s'", outputfile);
             exit(1);

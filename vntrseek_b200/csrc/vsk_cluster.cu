@@ -2,6 +2,7 @@
 // ClusterBasePrint (reference src/psearch1.91/cluster.h:268-332,452-541) over the
 // link records the device produced, in call order.  Host-only code.
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <unordered_map>
 
@@ -12,6 +13,7 @@ struct KeyRec {
     int32_t key;
     int32_t dir;
     int32_t cluster;
+    int8_t leftcon, rightcon;  // -r mode, hclust.h:825-847
 };
 struct Cluster {
     std::vector<int32_t> items;  // indices into keys, in append order
@@ -19,8 +21,23 @@ struct Cluster {
 };
 }  // namespace
 
+static int clusters_write(const vsk_link *links, int64_t n, const char *clu_path, const char *map_path,
+                          uint64_t *trcount, int option_r);
+
 extern "C" int vsk_clusters_write(const vsk_link *links, int64_t n, const char *clu_path, const char *map_path,
                                   uint64_t *trcount) {
+    return clusters_write(links, n, clu_path, map_path, trcount, 0);
+}
+
+// -r (ref-to-ref) flavour: members print as `key+` (a flank matched another TR exactly) or `key-`
+// (cluster.h:515-522), after the leftcon/rightcon marks of hclust.h:825-847 (MAXERRORS is 0 there)
+extern "C" int vsk_clusters_write_r(const vsk_link *links, int64_t n, const char *clu_path, const char *map_path,
+                                    uint64_t *trcount) {
+    return clusters_write(links, n, clu_path, map_path, trcount, 1);
+}
+
+static int clusters_write(const vsk_link *links, int64_t n, const char *clu_path, const char *map_path,
+                          uint64_t *trcount, int option_r) {
     std::vector<KeyRec> keys;
     std::vector<Cluster> clusters;  // creation order == print order
     std::unordered_map<int32_t, int32_t> by_key;
@@ -29,7 +46,7 @@ extern "C" int vsk_clusters_write(const vsk_link *links, int64_t n, const char *
         return it == by_key.end() ? -1 : it->second;
     };
     auto insert = [&](int32_t cl, int32_t key, int dir) {
-        keys.push_back(KeyRec{key, dir, cl});
+        keys.push_back(KeyRec{key, dir, cl, 0, 0});
         by_key.emplace(key, (int32_t)keys.size() - 1);
         clusters[(size_t)cl].items.push_back((int32_t)keys.size() - 1);
     };
@@ -45,7 +62,7 @@ extern "C" int vsk_clusters_write(const vsk_link *links, int64_t n, const char *
             const double sim = (1.0 - (l.dsum) / (255.0 * l.sumw));
             fprintf(mf, "%d%c=>%d:%.2lf:%d:%d\n", l.refkey, (0 == dir) ? '\'' : '\"', l.readkey, sim, l.lerr, l.rerr);
         }
-        if (l.refkey == l.readkey) continue;
+        if (l.refkey == l.readkey) continue;  // ClusterBaseAddLink returns at once; so does the -r marking
         const int32_t k1 = find(l.refkey), k2 = find(l.readkey);
         if (k1 < 0 && k2 < 0) {
             clusters.emplace_back();
@@ -72,6 +89,11 @@ extern "C" int vsk_clusters_write(const vsk_link *links, int64_t n, const char *
         } else {
             insert(keys[(size_t)k2].cluster, l.refkey, keys[(size_t)k2].dir == 0 ? dir : !dir);
         }
+        if (option_r && abs(l.refkey) != abs(l.readkey)) {
+            KeyRec &a = keys[(size_t)find(l.refkey)], &b = keys[(size_t)find(l.readkey)];
+            if (l.lerr <= 0) a.leftcon = b.leftcon = 1;
+            if (l.rerr <= 0) a.rightcon = b.rightcon = 1;
+        }
     }
     if (mf) fclose(mf);
     if (trcount) *trcount = (uint64_t)keys.size();
@@ -81,8 +103,11 @@ extern "C" int vsk_clusters_write(const vsk_link *links, int64_t n, const char *
         for (const Cluster &c : clusters) {
             if (!c.alive) continue;
             fputc('@', fp);
-            for (int32_t it : c.items)
-                fprintf(fp, keys[(size_t)it].dir ? " %d\"" : " %d'", keys[(size_t)it].key);
+            for (int32_t it : c.items) {
+                const KeyRec &k = keys[(size_t)it];
+                if (option_r) fprintf(fp, (k.leftcon || k.rightcon) ? " %d+" : " %d-", k.key);
+                else fprintf(fp, k.dir ? " %d\"" : " %d'", k.key);
+            }
             fputc('\n', fp);
         }
         fclose(fp);

@@ -633,6 +633,7 @@ vsk_dp_pass_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
     }
 }
 
+template <bool RMODE>
 __global__ void __launch_bounds__(128)
 vsk_flank_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__restrict__ pairs,
                  const int4 *__restrict__ res, const int64_t *__restrict__ exp_off, int64_t npairs, int64_t nexp,
@@ -662,10 +663,20 @@ vsk_flank_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__restri
     const int ql = reads.leftlen[dp], qr = reads.rightlen[dp];
     const int maxl = maxerrors ? maxerrors : luts.flank_maxerr[ql];
     const int maxr = maxerrors ? maxerrors : luts.flank_maxerr[qr];
-    const int lerr = vsk_ed_device<VSK_ED_PSEARCH>(refs.fl + refs.fl_off[2 * rp], rl,
-                                                   reads.fl + reads.fl_off[2 * dp], min(ql, rl));
-    const int rerr = vsk_ed_device<VSK_ED_PSEARCH>(refs.fl + refs.fl_off[2 * rp + 1], rrl,
-                                                   reads.fl + reads.fl_off[2 * dp + 1], min(qr, rrl));
+    const uint8_t *rfl = refs.fl + refs.fl_off[2 * rp], *rfr = refs.fl + refs.fl_off[2 * rp + 1];
+    const uint8_t *qfl = reads.fl + reads.fl_off[2 * dp], *qfr = reads.fl + reads.fl_off[2 * dp + 1];
+    int lerr, rerr;
+    if (!RMODE) {  // refs vs reads (hclust.h:656-697): the read flank is cut to the reference flank's length
+        lerr = vsk_ed_device<VSK_ED_PSEARCH>(rfl, rl, qfl, min(ql, rl));
+        rerr = vsk_ed_device<VSK_ED_PSEARCH>(rfr, rrl, qfr, min(qr, rrl));
+    } else {       // refs vs refs (hclust.h:700-751): full lengths, then once more with the roles swapped
+        lerr = vsk_ed_device<VSK_ED_PSEARCH>(rfl, rl, qfl, ql);
+        rerr = vsk_ed_device<VSK_ED_PSEARCH>(rfr, rrl, qfr, qr);
+        if (lerr != -1 && rerr != -1 && !(lerr <= maxl && rerr <= maxr)) {
+            lerr = vsk_ed_device<VSK_ED_PSEARCH>(qfl, ql, rfl, rl);
+            rerr = vsk_ed_device<VSK_ED_PSEARCH>(qfr, qr, rfr, rrl);
+        }
+    }
     if (lerr == -1 || rerr == -1) atomicAdd(&stats[5], 1ull);  // hclust.h:690-694 quits
     vsk_link_rec r;
     r.refkey = refs.key[ma];
@@ -866,8 +877,12 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, S.get(&recs, (size_t)ne));
     VSK_CUDA(ctx, S.get(&recs2, (size_t)ne));
     VSK_CUDA(ctx, S.get(&lflags, (size_t)ne));
-    vsk_flank_kernel<<<blocks(ne, 128), 128, 0, st>>>(refs, reads, R->luts, pairs2, res, exp_off, ndp, ne,
-                                                      prm->maxerrors, recs, lflags, d_stats);
+    if (prm->option_r)
+        vsk_flank_kernel<true><<<blocks(ne, 128), 128, 0, st>>>(refs, reads, R->luts, pairs2, res, exp_off, ndp, ne,
+                                                                0, recs, lflags, d_stats);
+    else
+        vsk_flank_kernel<false><<<blocks(ne, 128), 128, 0, st>>>(refs, reads, R->luts, pairs2, res, exp_off, ndp, ne,
+                                                                 prm->maxerrors, recs, lflags, d_stats);
     ctx->launches++;
     size_t tb6 = 0;
     cub::DeviceSelect::Flagged(nullptr, tb6, recs, lflags, recs2, d_n, ne, st);
@@ -894,7 +909,8 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
                                        const vsk_proclu_params *prm, vsk_proclu_result **out) {
     if (!ctx || !R || !Q || !prm || !out) return VSK_ERR_ARG;
     *out = nullptr;
-    if (prm->option_r) return vsk_fail(ctx, VSK_ERR_ARG, "-r (ref-to-ref) mode is not supported by the GPU path yet");
+    if (prm->option_r && prm->maxerrors != 0)  // psearch.c:995-999
+        return vsk_fail(ctx, VSK_ERR_ARG, "maxerror must be 0 because it will be dynamically generated based on flank length.");
     VSK_CUDA(ctx, cudaSetDevice(ctx->device));
     keep_pool(ctx);
     const vsk_trset *hq = Q->host;
