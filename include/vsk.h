@@ -263,6 +263,17 @@ int vsk_flank_pairs(vsk_ctx *ctx, const char *pool, int64_t pool_bytes, const vs
                     const vsk_flank *reads, int32_t nread, const int32_t *pair_read, const int32_t *pair_ref,
                     int64_t npairs, int maxerrors, uint32_t *out, float *kernel_ms);
 
+/* ---- refflankalign ----------------------------------------------------------------------
+ * Everything refflankalign.exe does after argv (reference
+ * src/newrefflankalign/refflankalign.c:379-1074): `<xmldir>/<a>_<b>.xml` per block and
+ * `<outdir>/representatives.txt`.  MAXERRORS <= 31 on the GPU build.                    */
+int vsk_refflankalign_run(vsk_ctx *ctx, const char *outdir, const char *xmldir, const char *inputfile,
+                          int maxerrors, int patlen_size_err, int reflen, int64_t *n_blocks, int64_t *n_pairs);
+/* narrowbandUnitCostDistanceSameLengthBestScoreLastRowColumnLowMemUsesPointers(a_i, b_i, maxerr)
+ * (src/newrefflankalign/narrowbandDistanceAlignment.c:533-776) for n string pairs           */
+int vsk_nbdist_pairs(vsk_ctx *ctx, const char *a, const int64_t *a_off, const char *b, const int64_t *b_off,
+                     int64_t n, int maxerr, int32_t *out);
+
 /* Edges mode (doEdgesBruteForce, psearch.c:1223-1405): `id1,id2` lines in, one
  * `id1{'|"},id2,%.4lf` line per edge + `#ave:` out.                              */
 int vsk_edges_run(vsk_ctx *ctx, const vsk_trset *a, const vsk_trset *b, const char *edgein_path,
