@@ -369,7 +369,7 @@ def ours(args, rank, world, local_rank):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                          "frac": achieved_gbs / peaks.get("hbm_gbs", 1.0), "traffic": None,
-                         "kernel": "vsk_dp_kernel", "kernel_ms_per_step": dp_ms / K,
+                         "kernel": "vsk_dp_kernel (+ vsk_dp_q8_kernel, vsk_dp_tiny_kernel: the three size classes of the profile DP)", "kernel_ms_per_step": dp_ms / K,
                          "kernel_share_of_step": (dp_ms / K) / step_ms, "peak_source": peak_src,
                          "note": "integer DP: issue/ALU bound, HBM fraction is evidence of non-boundness; see int_alu"},
             "int_alu": {"achieved": int_ops, "peak": int_peak, "unit": "Gop/s", "frac": int_ops / int_peak if int_peak else None,
