@@ -348,6 +348,7 @@ vsk_seed_kernel(DevTR reads, DevIndex idx, DevLuts luts, int32_t p_begin, int32_
             w.s = w.e2 = 0;
             w.extra = 0;
             bool found = false;
+            uint64_t code = ~0ull;  // no window position (cannot equal a real code: those use < 60 bits)
             if (i < len) {
                 uint32_t c1 = 0, c2 = 0;
                 for (int k = 0; k < nones; ++k) {
@@ -355,12 +356,19 @@ vsk_seed_kernel(DevTR reads, DevIndex idx, DevLuts luts, int32_t p_begin, int32_
                     if (k <= 14) c1 = c1 * 4 + b;
                     else c2 = c2 * 4 + b;
                 }
-                found = seed_lookup(idx, t, ((uint64_t)c1 << 32) | c2, lo, hi, w);
+                code = ((uint64_t)c1 << 32) | c2;
             }
+            // periodic (low-complexity) consensus strings repeat the same seed code every few positions:
+            // only the first lane of each group of equal codes looks the bucket up and emits keys; the
+            // CandidatesConsidered counter still counts the window once per position (`mult` lanes)
+            const unsigned same = __match_any_sync(0xffffffffu, code);
+            const bool leader = (i < len) && (lane == __ffs(same) - 1);
+            const int mult = __popc(same);
+            if (leader) found = seed_lookup(idx, t, code, lo, hi, w);
             const int64_t nd = found ? (w.e2 - w.s + w.extra) : 0;
             if (!FILL) {
                 emit += nd;
-                if (found) raw += idx.e_gcum[w.e2] - idx.e_gcum[w.s] + w.extra;
+                if (found) raw += (int64_t)mult * (idx.e_gcum[w.e2] - idx.e_gcum[w.s] + w.extra);
             } else {
                 // exclusive prefix of nd over the warp
                 int64_t incl = nd;
