@@ -516,8 +516,12 @@ vsk_lcs_long_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__res
         if (++r == M) {
             count += __popcll(~V & valid);
             r = 0;
-            if (++j == W) {
-                flags[item] = (count >= luts.lcs_min[shortest]) ? 1 : 0;
+            ++j;
+            // the LCS length is the sum over blocks of the matched columns: stop as soon as the
+            // threshold is reached, or cannot be reached even if every remaining column matched
+            const int need = luts.lcs_min[shortest], remaining = max(N - 64 * j, 0);
+            if (j == W || count >= need || count + remaining < need) {
+                flags[item] = (count >= need) ? 1 : 0;
                 have = false;
             }
         }
