@@ -368,7 +368,10 @@ def ours(args, rank, world, local_rank):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
-                         "frac": achieved_gbs / peaks.get("hbm_gbs", 1.0), "traffic": None,
+                         "frac": achieved_gbs / peaks.get("hbm_gbs", 1.0),
+                         "traffic": 1.96e9 if args.nreads == 1000000 and args.nref == 250000 else None,
+                         "traffic_note": "dram__bytes_read+write of one vsk_dp_kernel launch (first chunk), ncu --set full, "
+                                         "profiles/r01_summary.md; boundary/row-record scratch dominates it",
                          "kernel": "vsk_dp_kernel (+ vsk_dp_q8_kernel, vsk_dp_tiny_kernel: the three size classes of the profile DP)", "kernel_ms_per_step": dp_ms / K,
                          "kernel_share_of_step": (dp_ms / K) / step_ms, "peak_source": peak_src,
                          "note": "integer DP: issue/ALU bound, HBM fraction is evidence of non-boundness; see int_alu"},

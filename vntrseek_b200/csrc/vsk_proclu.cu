@@ -37,6 +37,7 @@ struct DevTR {
     // cons_codes[2*b + k]  = 2-bit codes of characters 32k..32k+31 of block b
     int64_t *cons_blk = nullptr;  // [2n+1] first block of every profile's consensus
     uint64_t *cons_planes = nullptr, *cons_codes = nullptr;
+    uint64_t *cons_cnt = nullptr;  // [2n] number of A, C, G, T in the consensus, 16 bits each
 };
 
 struct DevIndex {
@@ -102,6 +103,7 @@ __global__ void __launch_bounds__(256) vsk_pack_consensus_kernel(DevTR t, int64_
     const int len = (int)(t.cons_off[p + 1] - t.cons_off[p]);
     const int64_t b0 = t.cons_blk[p];
     const int nblk = (len + 63) >> 6;
+    uint64_t cnt = 0;
     for (int b = 0; b < nblk; ++b) {
         uint32_t pl[2][4];
         uint64_t code[2];
@@ -117,9 +119,12 @@ __global__ void __launch_bounds__(256) vsk_pack_consensus_kernel(DevTR t, int64_
             for (int l = 0; l < 32; ++l) w |= ((uint64_t)((lo >> l) & 1u) | ((uint64_t)((hi >> l) & 1u) << 1)) << (2 * l);
             code[h] = w;
         }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) cnt += (uint64_t)(__popc(pl[0][k]) + __popc(pl[1][k])) << (16 * k);
         if (lane < 4) t.cons_planes[4 * (b0 + b) + lane] = (uint64_t)pl[0][lane] | ((uint64_t)pl[1][lane] << 32);
         if (lane < 2) t.cons_codes[2 * (b0 + b) + lane] = code[lane];
     }
+    if (lane == 0) t.cons_cnt[p] = cnt;
 }
 
 static int upload_raw(vsk_ctx *ctx, std::vector<void *> &allocs, const uint8_t *h, size_t n, uint8_t **d,
@@ -171,6 +176,8 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
         r->allocs.push_back(r->d.cons_planes);
         VSK_CUDA(ctx, cudaMallocAsync((void **)&r->d.cons_codes, sizeof(uint64_t) * 2 * (size_t)(nblk + 1), ctx->stream));
         r->allocs.push_back(r->d.cons_codes);
+        VSK_CUDA(ctx, cudaMallocAsync((void **)&r->d.cons_cnt, sizeof(uint64_t) * (np + 1), ctx->stream));
+        r->allocs.push_back(r->d.cons_cnt);
         if (np) {
             vsk_pack_consensus_kernel<<<(unsigned)((np * 32 + 255) / 256), 256, 0, ctx->stream>>>(r->d, (int64_t)np);
             ctx->launches++;
@@ -425,9 +432,22 @@ vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__r
     const int M = ref_is_text ? mr : nr;
     const int shortest = M;
     if (N <= 63 && N > 60) N = 60;
+    // a common subsequence cannot use more copies of a base than either string has: pairs whose
+    // composition bound is already below the threshold fail without running the recurrence
+    bool decided = false;
+    if (in_range) {
+        const uint64_t ca = refs.cons_cnt[h], cb = reads.cons_cnt[p];
+        int bound = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) bound += min((int)((ca >> (16 * k)) & 0xffffu), (int)((cb >> (16 * k)) & 0xffffu));
+        if (bound < luts.lcs_min[shortest]) {
+            flags[i] = 0;
+            decided = true;
+        }
+    }
     // more than one block: left to vsk_lcs_long_kernel (work queue), which keeps this kernel's warps
     // uniform; one counter update per warp
-    const bool is_long = in_range && N > 64;
+    const bool is_long = in_range && !decided && N > 64;
     const unsigned lmask = __ballot_sync(0xffffffffu, is_long);
     if (lmask) {
         const int lane = threadIdx.x & 31, leader = __ffs(lmask) - 1;
@@ -439,7 +459,7 @@ vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__r
             flags[i] = 0;
         }
     }
-    if (!in_range || is_long) return;
+    if (!in_range || is_long || decided) return;
     const uint64_t *planes = ref_is_text ? refs.cons_planes + 4 * refs.cons_blk[h] : reads.cons_planes + 4 * reads.cons_blk[p];
     const uint64_t *codes = ref_is_text ? reads.cons_codes + 2 * reads.cons_blk[p] : refs.cons_codes + 2 * refs.cons_blk[h];
     uint64_t pl[4];
