@@ -62,6 +62,13 @@ extern "C" int vsk_init(vsk_ctx **out, int device, const uint8_t *sm) {
     VSK_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     VSK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    {  // freed stream-ordered memory stays in the pool: the work buffers are re-used launch after launch
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+            uint64_t thr = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+        }
+    }
     // symmetric expansion of the triangular table (EVALDISTANCE, profile.h:1100-1103)
     std::vector<uint8_t> full((size_t)VSK_NIDS * VSK_DROW, 0);
     for (int r = 0; r < VSK_NIDS; ++r)
@@ -102,6 +109,10 @@ extern "C" void vsk_destroy(vsk_ctx *ctx) {
     cudaFree(ctx->d_dp_scratch);
     cudaFree(ctx->d_tiny_dense);
     cudaFree(ctx->d_tiny_ktab);
+    for (int i = 0; i < 2; ++i)
+        if (ctx->dd_stream[i]) cudaStreamDestroy(ctx->dd_stream[i]);
+    for (int i = 0; i < 4; ++i)
+        if (ctx->dd_ev[i]) cudaEventDestroy(ctx->dd_ev[i]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

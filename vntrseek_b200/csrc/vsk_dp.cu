@@ -24,6 +24,8 @@
 // band (profile.h:1850-1877), so they never win or tie against in-band cells.
 #include <algorithm>
 
+#include <cstdlib>
+
 #include "vsk_internal.cuh"
 
 #define DP_WARPS 4
@@ -232,10 +234,11 @@ __global__ void __launch_bounds__(DP_WARPS * 32)
 vsk_dp_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
               const vsk_dp_job *__restrict__ jobs, int n_jobs, const uint8_t *__restrict__ dist,
               const uint16_t *__restrict__ gapnd, int4 *scratch, int scratch_stride, int *queue,
-              int4 *out) {
+              int4 *out, const int *__restrict__ n_jobs_dev, int skip_dir) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (n_jobs_dev) n_jobs = *n_jobs_dev;  // pairs handed back by the direction-bit path
     DpWarpSmem &ws = reinterpret_cast<DpWarpSmem *>(smem + 2048)[warp];
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_gapnd[i] = gapnd[i];
     __syncthreads();
@@ -249,6 +252,7 @@ vsk_dp_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict_
         ji = __shfl_sync(FULLMASK, ji, 0);
         if (ji >= n_jobs) break;
         const vsk_dp_job job = jobs[ji];
+        if (skip_dir && VSK_DP_DIRJOB(job.l2)) continue;  // done by vsk_dp_dir_kernel + vsk_dp_trace_kernel
         const uint16_t *L = left_ids + job.left_off;
         const uint16_t *Tp = top_ids + job.top_off;
         const int l1 = job.l1, l2 = job.l2;
@@ -624,6 +628,12 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         VSK_CUDA(ctx, cudaEventCreate(&e1));
         VSK_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
     }
+    static const bool use_dir = [] {
+        const char *e = getenv("VSK_DP_DIR");
+        return !(e && e[0] == '0');
+    }();
+    int64_t grid_w = 0;
+    int stride_w = 0;
     if (n_warp > 0) {
         if (!g_dp_attr_set) {
             VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -646,10 +656,16 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
             VSK_CUDA(ctx, cudaMalloc(&ctx->d_dp_scratch, bytes));
             ctx->dp_scratch_bytes = bytes;
         }
+        grid_w = grid;
+        stride_w = stride;
+        if (use_dir) {  // the direction-bit path forks here and overlaps the three kernels below
+            int rc = vsk_dp_dir_begin(ctx);
+            if (rc) return rc;
+        }
         VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
         vsk_dp_kernel<<<(unsigned)grid, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
             d_left_ids, d_top_ids, d_jobs, (int)n_warp, ctx->d_dist, ctx->d_gapnd,
-            (int4 *)ctx->d_dp_scratch, stride, ctx->d_queue, d_out);
+            (int4 *)ctx->d_dp_scratch, stride, ctx->d_queue, d_out, nullptr, use_dir ? 1 : 0);
         ctx->launches++;
         VSK_CUDA(ctx, cudaGetLastError());
     }
@@ -687,6 +703,22 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
             ctx->d_gapnd, d_out);
         ctx->launches++;
         VSK_CUDA(ctx, cudaGetLastError());
+    }
+    if (n_warp > 0 && use_dir) {
+        vsk_dp_job *d_redo = nullptr;
+        int *d_redo_n = nullptr;
+        int rc = vsk_dp_dir_launch(ctx, d_left_ids, d_top_ids, d_jobs, n_warp, max_l1, d_out, &d_redo, &d_redo_n);
+        if (rc) return rc;
+        if (d_redo) {  // pairs whose corner the band does not reach
+            VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
+            vsk_dp_kernel<<<(unsigned)grid_w, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
+                d_left_ids, d_top_ids, d_redo, 0, ctx->d_dist, ctx->d_gapnd, (int4 *)ctx->d_dp_scratch, stride_w,
+                ctx->d_queue, d_out, d_redo_n, 0);
+            ctx->launches++;
+            VSK_CUDA(ctx, cudaGetLastError());
+            VSK_CUDA(ctx, cudaFreeAsync(d_redo, ctx->stream));
+            VSK_CUDA(ctx, cudaFreeAsync(d_redo_n, ctx->stream));
+        }
     }
     if (ctx->profile) {
         VSK_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
@@ -767,7 +799,7 @@ extern "C" int vsk_pair_dp_static(vsk_ctx *ctx, const uint16_t *d_left_ids, int6
     if (grid > VSK_STATIC_CTAS) grid = VSK_STATIC_CTAS;
     vsk_dp_kernel<<<(unsigned)grid, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
         d_left_ids, d_top_ids, S->jobs, (int)n, ctx->d_dist, ctx->d_gapnd, S->boundary, VSK_STATIC_MAX_ROWS,
-        S->queue, reinterpret_cast<int4 *>(d_out));
+        S->queue, reinterpret_cast<int4 *>(d_out), nullptr, 0);
     ctx->launches++;
     VSK_CUDA(ctx, cudaGetLastError());
     VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

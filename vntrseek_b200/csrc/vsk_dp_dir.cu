@@ -1,0 +1,547 @@
+// Profile DP for the long pairs, in two kernels: a forward sweep that keeps only the distance
+// per cell and writes the chosen direction (2 bits per cell) to HBM, and a trace that walks the
+// directions back from the corner and sums dashnum*cost / dashnum along the path -- literally what
+// GetFixedProfileAP / GetFixedProfileAPNarrowband do (reference src/psearch1.91/profile.h:2092-2210,
+// 1828-2009), except that the matrix holds 2-bit directions instead of 8-byte cells.
+//
+// Why: the one-kernel variant in vsk_dp.cu carries the two path sums with every cell, which is half
+// of its ~20 instructions per cell and three quarters of its per-lane state.  Dropping them lets a
+// lane own 16 columns (strips of 512) at fewer registers, i.e. fewer instructions per cell and less
+// per-step overhead.  The trace costs L1+L2 dependent steps per pair, run one pair per thread.
+//
+// Direction words: one uint32 per (row, lane) of a strip = the CPL (8, 12 or 16, chosen per pair by
+// dd_plan so that the strips fit the pair) cells of that lane; cell j holds "not diagonal" in bit
+// 2(CPL-1-j)+1 and "right rather than down" in bit 2(CPL-1-j).  A lane finishes row R at step R+lane; it
+// parks the word in a private shared-memory delay line and every lane stores its word of row R at
+// step R+31, so the 32 words of a row go out as one 128-byte line.
+#include <algorithm>
+#include <cstdlib>
+
+#include <cub/cub.cuh>
+
+#include "vsk_internal.cuh"
+
+#define DD_WARPS 4
+#define DD_TBYTES 8192
+#define DD_MAXCPL 16
+#define DD_STEP_OV 3  // cost of a wavefront step that does not depend on the cells per lane, in cells
+#define DD_FULL 0xffffffffu
+
+struct DdWarpSmem {
+    uint8_t T[DD_TBYTES];   // compact substitution table [na][nb]
+    uint8_t mapL[1024];     // composition id -> local row index
+    uint32_t bmL[32], bmT[32];
+    uint16_t preT[32];
+    uint16_t invL[256], invT[256];
+    uint32_t ring[32][32];  // per-lane delay line of direction words, [row & 31][lane]
+};
+#define DD_SMEM_BYTES (2048 + DD_WARPS * sizeof(DdWarpSmem))
+
+// columns per lane and number of column strips of a pair: the cheapest of 8, 12, 16 columns per lane
+__host__ __device__ inline void dd_plan(int l1, int l2, int &cpl, int &ns) {
+    int best = 0x7fffffff;
+    cpl = 16;
+    ns = 1;
+#pragma unroll
+    for (int c = 16; c >= 8; c -= 4) {
+        const int n = (l2 + 32 * c - 1) / (32 * c);
+        const int cost = n * (c + DD_STEP_OV);  // x (l1 + 31) steps either way
+        if (cost < best) {
+            best = cost;
+            cpl = c;
+            ns = n;
+        }
+    }
+    (void)l1;
+}
+
+// row record: bits 0..15 table row offset (local index * nb, or the id for the global table),
+// 16..23 gap cost d(0,l)
+__device__ __forceinline__ uint32_t dd_pack_row(int off, int gn) {
+    return (uint32_t)off | ((uint32_t)(gn & 255) << 16);
+}
+
+// local alphabets, compact table, row records (same scheme as vsk_dp_kernel); returns nb, smemt
+__device__ __forceinline__ bool dd_setup(const uint16_t *__restrict__ L, const uint16_t *__restrict__ Tp, int l1, int l2,
+                                         const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
+                                         uint32_t *rowrec, int &nb_out) {
+    const int lane = threadIdx.x & 31;
+    ws.bmL[lane] = 0;
+    ws.bmT[lane] = 0;
+    __syncwarp();
+    for (int i = lane; i < l1; i += 32) {
+        const int id = L[i];
+        atomicOr(&ws.bmL[id >> 5], 1u << (id & 31));
+    }
+    for (int i = lane; i < l2; i += 32) {
+        const int id = Tp[i];
+        atomicOr(&ws.bmT[id >> 5], 1u << (id & 31));
+    }
+    __syncwarp();
+    const uint32_t bl = ws.bmL[lane], bt = ws.bmT[lane];
+    int xl = __popc(bl), xt = __popc(bt);
+    const int cl = xl, ct = xt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int a = __shfl_up_sync(DD_FULL, xl, o);
+        const int b = __shfl_up_sync(DD_FULL, xt, o);
+        if (lane >= o) { xl += a; xt += b; }
+    }
+    const int na = __shfl_sync(DD_FULL, xl, 31), nb = __shfl_sync(DD_FULL, xt, 31);
+    const bool smemt = (na <= 256) && (nb <= 256) && (na * nb <= DD_TBYTES);
+    if (smemt) {
+        ws.preT[lane] = (uint16_t)(xt - ct);
+        uint32_t b = bl;
+        int rk = xl - cl;
+        while (b) {
+            const int id = lane * 32 + __ffs(b) - 1;
+            b &= b - 1;
+            ws.mapL[id] = (uint8_t)rk;
+            ws.invL[rk] = (uint16_t)id;
+            ++rk;
+        }
+        b = bt;
+        rk = xt - ct;
+        while (b) {
+            const int id = lane * 32 + __ffs(b) - 1;
+            b &= b - 1;
+            ws.invT[rk] = (uint16_t)id;
+            ++rk;
+        }
+        __syncwarp();
+#pragma unroll 4
+        for (int a = 0; a < na; ++a) {
+            const uint8_t *drow = dist + (int)ws.invL[a] * VSK_DROW;
+            for (int c = lane; c < nb; c += 32) ws.T[a * nb + c] = __ldg(drow + ws.invT[c]);
+        }
+        __syncwarp();
+    }
+    for (int i = lane; i < l1; i += 32) {
+        const int id = L[i];
+        rowrec[i] = dd_pack_row(smemt ? (int)ws.mapL[id] * nb : id, s_gapnd[id]);
+    }
+    __syncwarp();
+    nb_out = nb;
+    return smemt;
+}
+
+template <int CPL, bool MASKED, bool SMEMT>
+__device__ __forceinline__ uint32_t dd_row_cells(int (&Hd)[CPL], const int (&tb)[CPL], const int (&gt)[CPL], int dgd,
+                                                 int lfd, const uint8_t *__restrict__ trow, int gl, int lo, int hi) {
+    uint32_t w = 0;
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+        const int upd = Hd[j];
+        const int dlt = SMEMT ? (int)trow[tb[j]] : (int)__ldg(trow + tb[j]);
+        const int sa = dgd + dlt;   // diagonal
+        const int f = upd + gl;     // down
+        const int e = lfd + gt[j];  // right
+        // min3switch (profile.h:1098-1099): diag if sa<=f && sa<=e; else down if f<=e; else right.
+        // d = min3, so "not diagonal" is the sign of d - sa and "right" is the sign of e - f.
+        int d = min(min(sa, f), e);
+        w = __funnelshift_l((uint32_t)(d - sa), w, 1);
+        w = __funnelshift_l((uint32_t)(e - f), w, 1);
+        if (MASKED) {
+            if (j < lo || j > hi) d = VSK_BIG;
+        }
+        dgd = upd;
+        Hd[j] = d;
+        lfd = d;
+    }
+    return w;
+}
+
+template <int CPL, bool SMEMT>
+__device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *__restrict__ Tp,
+                                        const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
+                                        int nb, int *bscr, const uint32_t *rowrec, uint32_t *__restrict__ dir,
+                                        int4 *out) {
+    const int lane = threadIdx.x & 31;
+    const int l1 = job.l1, l2 = job.l2, br = job.br;
+    const bool banded = br >= 0;
+    const double sv = job.svector;
+    const int npass = (l2 + (32 * CPL) - 1) / (32 * CPL);
+    int totd = 0;
+    int Hd[CPL];
+    int prev_r_hi = l1;
+
+    for (int pass = 0; pass < npass; ++pass) {
+        const int cbase = pass * (32 * CPL) + lane * CPL;
+        int tb[CPL], gt[CPL];
+        int sd = 0;
+#pragma unroll
+        for (int j = 0; j < CPL; ++j) {
+            const int c = cbase + j;
+            const int id = (c < l2) ? (int)Tp[c] : 0;
+            const int g = s_gapnd[id] & 255;
+            gt[j] = g;
+            if (SMEMT) {
+                const int w = id >> 5;
+                tb[j] = ws.preT[w] + __popc(ws.bmT[w] & ((1u << (id & 31)) - 1u));
+            } else {
+                tb[j] = id;
+            }
+            sd += g;
+            Hd[j] = sd;
+        }
+        int xd = sd;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int a = __shfl_up_sync(DD_FULL, xd, o);
+            if (lane >= o) xd += a;
+        }
+        const int ed = xd - sd + totd;
+#pragma unroll
+        for (int j = 0; j < CPL; ++j) {
+            Hd[j] += ed;
+            if (banded && cbase + j + 1 > br) Hd[j] = VSK_BIG;  // profile.h:1801-1802
+        }
+        int dgd = ed;
+        if (banded && cbase > br) dgd = VSK_BIG;
+        totd += __shfl_sync(DD_FULL, xd, 31);
+
+        // rows whose band can touch this strip (conservative; the per-cell mask stays exact)
+        int r_lo = 0, r_hi = l1;
+        if (banded) {
+            const int c0 = pass * (32 * CPL);
+            const double a = (double)(c0 + 1 - br), b = (double)(min(l2, c0 + (32 * CPL)) + br + 1);
+            r_lo = max(0, (int)floor(a / sv) - 2);
+            r_hi = min(l1, (int)ceil(b / sv) + 2);
+            if (r_hi < r_lo) r_hi = r_lo;
+        }
+        if (r_lo > 0) {
+#pragma unroll
+            for (int j = 0; j < CPL; ++j) Hd[j] = VSK_BIG;
+            dgd = VSK_BIG;
+        }
+        const bool rd_scratch = (lane == 0) && (pass > 0);
+        const bool wr_scratch = (lane == 31) && (pass < npass - 1);
+        int nxt = VSK_BIG;
+        if (rd_scratch && r_lo < prev_r_hi) nxt = __ldcg(bscr + r_lo);
+        uint32_t rec_next = __ldcg(rowrec + min(max(r_lo - lane, 0), l1 - 1));
+        uint32_t *dstrip = dir + (size_t)pass * l1 * 32 + lane;
+
+        auto step = [&](const int s, const bool check) {
+            const int r = s - lane;
+            int lfd = __shfl_up_sync(DD_FULL, Hd[CPL - 1], 1);
+            const bool active = !check || ((r >= r_lo) && (r < r_hi));
+            const uint32_t rec = rec_next;
+            rec_next = __ldcg(rowrec + min(max(r + 1, 0), l1 - 1));
+            const int gl = (rec >> 16) & 255;
+            const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
+            int lo = 0, hi = CPL;
+            bool need_mask = false;
+            if (active) {
+                if (lane == 0) {
+                    if (pass == 0) {
+                        lfd = dgd + gl;  // column 0, profile.h:2084-2090
+                    } else {
+                        lfd = nxt;
+                        nxt = (r + 1 < prev_r_hi) ? __ldcg(bscr + r + 1) : VSK_BIG;
+                    }
+                }
+                if (banded) {  // profile.h:1835-1839
+                    const int center = __double2int_rz(__dmul_rn((double)(r + 1), sv));
+                    lo = max(1, center - br) - (cbase + 1);
+                    hi = min(l2, center + br) - (cbase + 1);
+                    need_mask = (lo > 0) || (hi < CPL - 1);
+                }
+            }
+            const bool anymask = banded && __any_sync(DD_FULL, need_mask);
+            if (active) {
+                uint32_t w;
+                if (anymask) w = dd_row_cells<CPL, true, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl, lo, hi);
+                else w = dd_row_cells<CPL, false, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl, lo, hi);
+                dgd = lfd;
+                ws.ring[r & 31][lane] = w;
+                if (wr_scratch) bscr[r] = Hd[CPL - 1];
+            }
+            // every lane's word of row s-31 is in its delay line now: one 128-byte line goes out
+            const int ro = s - 31;
+            if (ro >= r_lo && ro < r_hi) dstrip[(size_t)ro * 32] = ws.ring[ro & 31][lane];
+        };
+        const int s_fill_end = min(r_lo + 31, r_hi + 31);
+        int s = r_lo;
+        for (; s < s_fill_end; ++s) step(s, true);
+        for (; s < r_hi; ++s) step(s, false);
+        for (; s < r_hi + 31; ++s) step(s, true);
+        prev_r_hi = r_hi;
+        __syncwarp();
+    }
+    const int cl = (l2 - 1) - (npass - 1) * (32 * CPL);
+    if (lane == cl / CPL) {
+        const int jr = cl % CPL;
+#pragma unroll
+        for (int j = 0; j < CPL; ++j)
+            if (j == jr) out[job.out_idx] = make_int4(Hd[j], 0, 0, 0);
+    }
+}
+
+// forward sweep: jobs[0..n) with their direction-word offsets dir_off[] into dirbuf
+__global__ void __launch_bounds__(DD_WARPS * 32)
+vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
+                  const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
+                  const int *__restrict__ bounds, int batch, int64_t batch_words, const uint8_t *__restrict__ dist,
+                  const uint16_t *__restrict__ gapnd, int *scratch, int scratch_stride, uint32_t *__restrict__ dirbuf,
+                  int *queue, int4 *out) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(smem);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    DdWarpSmem &ws = reinterpret_cast<DdWarpSmem *>(smem + 2048)[warp];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_gapnd[i] = gapnd[i];
+    __syncthreads();
+    // per-warp scratch slice: scratch_stride boundary distances + scratch_stride row records
+    int *my_bscr = scratch + (size_t)(blockIdx.x * DD_WARPS + warp) * 2 * scratch_stride;
+    uint32_t *my_rowrec = reinterpret_cast<uint32_t *>(my_bscr + scratch_stride);
+    const int lo_job = bounds[batch], hi_job = bounds[batch + 1];
+    for (;;) {
+        int ji = 0;
+        if (lane == 0) ji = lo_job + atomicAdd(queue + batch, 1);
+        ji = __shfl_sync(DD_FULL, ji, 0);
+        if (ji >= hi_job) break;
+        const vsk_dp_job job = jobs[ji];
+        if (!VSK_DP_DIRJOB(job.l2)) continue;
+        const uint16_t *L = left_ids + job.left_off;
+        const uint16_t *Tp = top_ids + job.top_off;
+        int nb = 0;
+        const bool smemt = dd_setup(L, Tp, job.l1, job.l2, dist, s_gapnd, ws, my_rowrec, nb);
+        uint32_t *dir = dirbuf + (dir_off[ji] - (int64_t)batch * batch_words);
+        int cpl, ns;
+        dd_plan(job.l1, job.l2, cpl, ns);
+#define DD_DISPATCH(C)                                                                       \
+    do {                                                                                     \
+        if (smemt) dd_pair<C, true>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out); \
+        else dd_pair<C, false>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out);      \
+    } while (0)
+        if (cpl == 16) DD_DISPATCH(16);
+        else if (cpl == 12) DD_DISPATCH(12);
+        else DD_DISPATCH(8);
+#undef DD_DISPATCH
+        __syncwarp();
+    }
+}
+
+// Trace: one thread per pair walks the stored directions from (l1,l2) to (0,0) and sums what the
+// reference's traceback sums (profile.h:2135-2210): dashnum*cost, dashnum, path length.  Pairs whose
+// corner is unreachable (distance >= BIG: the band is disconnected) are handed back on `redo`; the
+// one-kernel variant defines their result.
+#define DT_THREADS 128
+
+__global__ void __launch_bounds__(DT_THREADS)
+vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
+                    const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
+                    const int *__restrict__ bounds, int batch, int64_t batch_words, const uint8_t *__restrict__ dist,
+                    const uint16_t *__restrict__ gapnd, const uint32_t *__restrict__ dirbuf, int4 *out,
+                    vsk_dp_job *redo, int *redo_count) {
+    __shared__ uint16_t s_gapnd[1024];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_gapnd[i] = gapnd[i];
+    __syncthreads();
+    const int lo_job = bounds[batch], hi_job = bounds[batch + 1];
+    for (int ji = lo_job + blockIdx.x * blockDim.x + threadIdx.x; ji < hi_job; ji += gridDim.x * blockDim.x) {
+        const vsk_dp_job job = jobs[ji];
+        if (!VSK_DP_DIRJOB(job.l2)) continue;
+        const int d = out[job.out_idx].x;
+        if (d >= VSK_BIG) {
+            redo[atomicAdd(redo_count, 1)] = job;
+            continue;
+        }
+        const uint16_t *L = left_ids + job.left_off;
+        const uint16_t *Tp = top_ids + job.top_off;
+        const uint32_t *dir = dirbuf + (dir_off[ji] - (int64_t)batch * batch_words);
+        const int l1 = job.l1;
+        int cpl, ns;
+        dd_plan(job.l1, job.l2, cpl, ns);
+        int r = job.l1, c = job.l2;
+        int p1 = 0, sumw = 0, len = 0;
+        // position of column c-1 inside the strips: strip*32 + lane, cell
+        int sl = (c - 1) / cpl, j = (c - 1) - sl * cpl;
+        uint32_t w = 0;
+        int wr = -1, wl = -1;  // (row, strip*32+lane) of the cached word
+        while (r > 0 && c > 0) {
+            if (wr != r || wl != sl) {
+                w = __ldcs(dir + ((size_t)(sl >> 5) * l1 + (r - 1)) * 32 + (sl & 31));
+                wr = r;
+                wl = sl;
+            }
+            const uint32_t bits = (w >> (2 * (cpl - 1 - j))) & 3u;  // bit 1: not diagonal, bit 0: right
+            const int idl = L[r - 1], idt = Tp[c - 1];
+            const int gnl = s_gapnd[idl], gnt = s_gapnd[idt];
+            bool left = false;
+            if (!(bits & 2u)) {
+                int dn = (gnl >> 8) + (gnt >> 8);
+                dn = dn < 10 ? dn : 10;
+                p1 += dn * (int)__ldg(dist + idl * VSK_DROW + idt);
+                sumw += dn;
+                --r;
+                left = true;
+            } else if (!(bits & 1u)) {
+                p1 += (gnl >> 8) * (gnl & 255);
+                sumw += gnl >> 8;
+                --r;
+            } else {
+                p1 += (gnt >> 8) * (gnt & 255);
+                sumw += gnt >> 8;
+                left = true;
+            }
+            if (left) {
+                --c;
+                if (--j < 0) {
+                    j = cpl - 1;
+                    --sl;
+                }
+            }
+            ++len;
+        }
+        for (; r > 0; --r, ++len) {  // column 0: gaps in the top profile
+            const int gnl = s_gapnd[L[r - 1]];
+            p1 += (gnl >> 8) * (gnl & 255);
+            sumw += gnl >> 8;
+        }
+        for (; c > 0; --c, ++len) {  // row 0: gaps in the left profile
+            const int gnt = s_gapnd[Tp[c - 1]];
+            p1 += (gnt >> 8) * (gnt & 255);
+            sumw += gnt >> 8;
+        }
+        out[job.out_idx] = make_int4(d, p1, sumw, len);
+    }
+}
+
+// direction words a job needs (0 = not a job for this path)
+__global__ void vsk_dd_words_kernel(const vsk_dp_job *__restrict__ jobs, int n, int64_t *__restrict__ words) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int l1 = jobs[i].l1, l2 = jobs[i].l2;
+    int cpl, ns;
+    dd_plan(l1, l2, cpl, ns);
+    words[i] = VSK_DP_DIRJOB(l2) ? (int64_t)ns * l1 * 32 : 0;
+}
+
+// bounds[b] = first job whose direction words start at or after b*batch_words (jobs of a batch are
+// [bounds[b], bounds[b+1])); bounds[nb] = n
+__global__ void vsk_dd_bounds_kernel(const int64_t *__restrict__ off, int n, int64_t batch_words, int nb,
+                                     int *__restrict__ bounds) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > nb) return;
+    if (b == nb) {
+        bounds[b] = n;
+        return;
+    }
+    const int64_t want = (int64_t)b * batch_words;
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (off[mid] >= want) hi = mid;
+        else lo = mid + 1;
+    }
+    bounds[b] = lo;
+}
+
+static int g_dd_attr_set = 0;
+
+int vsk_dp_dir_begin(vsk_ctx *ctx) {
+    for (int i = 0; i < 2; ++i)
+        if (!ctx->dd_stream[i]) VSK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->dd_stream[i], cudaStreamNonBlocking));
+    for (int i = 0; i < 4; ++i)
+        if (!ctx->dd_ev[i]) VSK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->dd_ev[i], cudaEventDisableTiming));
+    VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[0], ctx->stream));
+    return VSK_OK;
+}
+
+// Runs the jobs of d_jobs[0..n) that satisfy VSK_DP_DIRJOB through the two kernels above, in batches
+// whose direction words fit the buffer; the batches alternate between two side streams (each with
+// its own half of the buffer) that fork from the vsk_dp_dir_begin mark and join ctx->stream at the
+// end.  *redo / *redo_count (device, stream-ordered allocations the caller frees on ctx->stream)
+// receive the pairs that must go through vsk_dp_kernel; both stay null when no job qualified.
+int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids, const vsk_dp_job *d_jobs,
+                      int64_t n, int32_t max_l1, int4 *d_out, vsk_dp_job **redo, int **redo_count) {
+    *redo = nullptr;
+    *redo_count = nullptr;
+    if (n <= 0) return VSK_OK;
+    cudaStream_t s0 = ctx->dd_stream[0], s1 = ctx->dd_stream[1];
+    VSK_CUDA(ctx, cudaStreamWaitEvent(s0, ctx->dd_ev[0], 0));
+    int64_t *d_words = nullptr, *d_off = nullptr;
+    VSK_CUDA(ctx, cudaMallocAsync(&d_words, (size_t)(n + 1) * sizeof(int64_t), s0));
+    VSK_CUDA(ctx, cudaMallocAsync(&d_off, (size_t)(n + 1) * sizeof(int64_t), s0));
+    VSK_CUDA(ctx, cudaMemsetAsync(d_words + n, 0, sizeof(int64_t), s0));
+    vsk_dd_words_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s0>>>(d_jobs, (int)n, d_words);
+    ctx->launches++;
+    size_t tmp_bytes = 0;
+    VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
+    void *d_tmp = nullptr;
+    VSK_CUDA(ctx, cudaMallocAsync(&d_tmp, tmp_bytes ? tmp_bytes : 16, s0));
+    VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
+    ctx->launches += 2;
+    int64_t total = 0;
+    VSK_CUDA(ctx, cudaMemcpyAsync(&total, d_off + n, sizeof(int64_t), cudaMemcpyDeviceToHost, s0));
+    VSK_CUDA(ctx, cudaStreamSynchronize(s0));
+    VSK_CUDA(ctx, cudaFreeAsync(d_tmp, s0));
+    VSK_CUDA(ctx, cudaFreeAsync(d_words, s0));
+    if (total == 0) {
+        VSK_CUDA(ctx, cudaFreeAsync(d_off, s0));
+        return VSK_OK;
+    }
+    // batch size: VSK_DIR_BATCH_MB of direction words per stream (default 4 GiB), at most a sixth of the free memory
+    int64_t batch_mb = 4096;
+    if (const char *e = getenv("VSK_DIR_BATCH_MB")) batch_mb = std::max<int64_t>(16, atoll(e));
+    size_t free_b = 0, total_b = 0;
+    VSK_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
+    const int64_t max_job_words = (int64_t)((VSK_MAXPROF + 255) / 256) * max_l1 * 32;  // strips are >= 256 columns
+    int64_t batch_words = std::min<int64_t>(batch_mb << 18, (int64_t)(free_b / 6 / 4));
+    batch_words = std::max<int64_t>(batch_words, max_job_words);
+    const int nb = (int)((total + batch_words - 1) / batch_words);
+    const int64_t half_words = (nb == 1) ? total : batch_words + max_job_words;
+    const int nhalf = nb == 1 ? 1 : 2;
+
+    if (!g_dd_attr_set) {
+        VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_dir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)DD_SMEM_BYTES));
+        g_dd_attr_set = 1;
+    }
+    int per_sm = 0;
+    VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_dir_kernel, DD_WARPS * 32,
+                                                                 DD_SMEM_BYTES));
+    if (per_sm < 1) per_sm = 1;
+    const int grid = ctx->sm_count * per_sm;
+    const int stride = ((max_l1 + 31) / 32) * 32;
+    const size_t scr_ints = (size_t)grid * DD_WARPS * 2 * stride;
+
+    uint32_t *d_dir = nullptr;
+    int *d_bounds = nullptr, *d_queue = nullptr, *d_scr = nullptr;
+    VSK_CUDA(ctx, cudaMallocAsync(&d_dir, (size_t)half_words * nhalf * 4, s0));
+    VSK_CUDA(ctx, cudaMallocAsync(&d_bounds, (size_t)(nb + 1) * sizeof(int), s0));
+    VSK_CUDA(ctx, cudaMallocAsync(&d_queue, (size_t)(nb + 1) * sizeof(int), s0));
+    VSK_CUDA(ctx, cudaMallocAsync(&d_scr, scr_ints * nhalf * sizeof(int), s0));
+    VSK_CUDA(ctx, cudaMallocAsync(redo, (size_t)n * sizeof(vsk_dp_job), s0));
+    VSK_CUDA(ctx, cudaMallocAsync(redo_count, sizeof(int), s0));
+    VSK_CUDA(ctx, cudaMemsetAsync(d_queue, 0, (size_t)(nb + 1) * sizeof(int), s0));
+    VSK_CUDA(ctx, cudaMemsetAsync(*redo_count, 0, sizeof(int), s0));
+    vsk_dd_bounds_kernel<<<(nb + 1 + 127) / 128, 128, 0, s0>>>(d_off, (int)n, batch_words, nb, d_bounds);
+    ctx->launches++;
+    VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[1], s0));
+    VSK_CUDA(ctx, cudaStreamWaitEvent(s1, ctx->dd_ev[1], 0));  // s1 starts after the buffers exist
+
+    for (int b = 0; b < nb; ++b) {
+        cudaStream_t st = (b & 1) ? s1 : s0;
+        uint32_t *dir = d_dir + (size_t)(b & 1) * half_words;
+        int *scr = d_scr + (size_t)(b & 1) * scr_ints;
+        vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, DD_SMEM_BYTES, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
+                                                                      batch_words, ctx->d_dist, ctx->d_gapnd, scr,
+                                                                      stride, dir, d_queue, d_out);
+        vsk_dp_trace_kernel<<<ctx->sm_count * 8, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
+                                                                       batch_words, ctx->d_dist, ctx->d_gapnd, dir,
+                                                                       d_out, *redo, *redo_count);
+        ctx->launches += 2;
+    }
+    VSK_CUDA(ctx, cudaGetLastError());
+    // join: ctx->stream continues after both side streams
+    VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[2], s0));
+    VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[3], s1));
+    VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[2], 0));
+    VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[3], 0));
+    VSK_CUDA(ctx, cudaFreeAsync(d_scr, ctx->stream));
+    VSK_CUDA(ctx, cudaFreeAsync(d_dir, ctx->stream));
+    VSK_CUDA(ctx, cudaFreeAsync(d_bounds, ctx->stream));
+    VSK_CUDA(ctx, cudaFreeAsync(d_queue, ctx->stream));
+    VSK_CUDA(ctx, cudaFreeAsync(d_off, ctx->stream));
+    return VSK_OK;
+}

@@ -33,6 +33,10 @@ struct vsk_ctx {
     void *d_dp_scratch = nullptr;
     size_t dp_scratch_bytes = 0;
     int *d_queue = nullptr;       // dynamic work counter
+    // side streams of the direction-bit DP path: batches alternate between them so that the tail of
+    // one forward sweep is filled by the next (created on first use)
+    cudaStream_t dd_stream[2] = {nullptr, nullptr};
+    cudaEvent_t dd_ev[4] = {nullptr, nullptr, nullptr, nullptr};
     std::vector<uint8_t> h_dist;  // host copy of the symmetric table
     // dense-alphabet tables of the thread-per-pair DP kernel, cached per id set
     vsk_idset tiny_key;
@@ -100,6 +104,14 @@ __host__ __device__ inline uint32_t vsk_dp_sort_key(int l1, int l2, int br) {
 int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids,
                   const vsk_dp_job *d_jobs, int64_t n_jobs, int64_t n_q8, int64_t n_tiny, int32_t max_l1,
                   const vsk_idset *ids, int4 *d_out);
+// Pairs with more than 128 columns go through the direction-bit kernels of vsk_dp_dir.cu (forward
+// sweep + trace); vsk_dp_kernel skips them when told so and takes the pairs handed back on `redo`.
+#define VSK_DP_DIRJOB(l2) ((l2) > 128)
+// vsk_dp_dir_begin marks the point of ctx->stream the side streams start from (call it before the
+// other DP kernels are enqueued so that they overlap); vsk_dp_dir_launch joins back into ctx->stream.
+int vsk_dp_dir_begin(vsk_ctx *ctx);
+int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids, const vsk_dp_job *d_jobs,
+                      int64_t n, int32_t max_l1, int4 *d_out, vsk_dp_job **redo, int **redo_count);
 // which composition ids occur in d_ids[0..n)
 int vsk_id_presence(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out);
 
