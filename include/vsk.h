@@ -226,6 +226,7 @@ int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *refs, const vsk_reads 
                             const vsk_proclu_params *prm, vsk_proclu_result **out);
 int64_t vsk_proclu_result_links(const vsk_proclu_result *r, const vsk_link **links);
 void vsk_proclu_result_stats(const vsk_proclu_result *r, vsk_proclu_stats *stats);
+/* The links live in page-locked memory owned by the context: free every result before vsk_destroy. */
 void vsk_proclu_result_free(vsk_proclu_result *r);
 
 /* ClusterBaseAddLink over the links in order + ClusterBasePrint (cluster.h:268-332,

@@ -272,9 +272,23 @@ def _stats_dict(st):
     return {name: int(getattr(st, name)) for name, _ in ProcluStats._fields_}
 
 
+class _ResultOwner:
+    """Frees a vsk_proclu_result when the last array that views its links goes away."""
+
+    def __init__(self, ctx, res):
+        self.ctx, self.res = ctx, res
+
+    def __del__(self):
+        if self.res and self.ctx.h:  # the links are the context's page-locked memory: not after close()
+            lib().vsk_proclu_result_free(self.res)
+        self.res = None
+
+
 def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=True, count_cells=False):
     """vsk_proclu_run (reads = TRSetHandle, host buffers) or vsk_proclu_run_resident
-    (reads = ResidentReads).  Returns (links structured array, stats dict)."""
+    (reads = ResidentReads).  Returns (links structured array, stats dict).  The array is a
+    view of the result's page-locked buffer (no copy); the buffer goes back to the
+    context when the array is dropped."""
     prm = ProcluParams(cutoff, maxerrors, 0, int(count_cells), key_budget)
     res = C.c_void_p()
     if isinstance(reads, ResidentReads):
@@ -289,9 +303,10 @@ def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=T
         n = lib().vsk_proclu_result_links(res, C.byref(ptr))
         if n:
             buf = (C.c_char * (n * LINK_DTYPE.itemsize)).from_address(ptr.value)
-            links = np.frombuffer(buf, dtype=LINK_DTYPE, count=n).copy()
-        else:
-            links = np.zeros(0, LINK_DTYPE)
+            buf._owner = _ResultOwner(ctx, res)
+            links = np.frombuffer(buf, dtype=LINK_DTYPE, count=n)
+            return links, _stats_dict(st)
+        links = np.zeros(0, LINK_DTYPE)
     lib().vsk_proclu_result_free(res)
     return links, _stats_dict(st)
 

@@ -113,8 +113,48 @@ extern "C" void vsk_destroy(vsk_ctx *ctx) {
         if (ctx->dd_stream[i]) cudaStreamDestroy(ctx->dd_stream[i]);
     for (int i = 0; i < 4; ++i)
         if (ctx->dd_ev[i]) cudaEventDestroy(ctx->dd_ev[i]);
+    for (auto &b : ctx->pin_free) cudaFreeHost(b.first);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+void *vsk_pin_get(vsk_ctx *ctx, size_t bytes, size_t *cap) {
+    if (bytes == 0) bytes = 1;
+    size_t best = ctx->pin_free.size();
+    for (size_t i = 0; i < ctx->pin_free.size(); ++i)  // smallest buffer that fits
+        if (ctx->pin_free[i].second >= bytes && (best == ctx->pin_free.size() || ctx->pin_free[i].second < ctx->pin_free[best].second))
+            best = i;
+    if (best < ctx->pin_free.size()) {
+        void *p = ctx->pin_free[best].first;
+        *cap = ctx->pin_free[best].second;
+        ctx->pin_free.erase(ctx->pin_free.begin() + (long)best);
+        return p;
+    }
+    const size_t want = ((bytes + bytes / 4) + 65535) & ~(size_t)65535;
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, want, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    *cap = want;
+    return p;
+}
+
+void vsk_pin_put(vsk_ctx *ctx, void *p, size_t cap) {
+    if (!p) return;
+    if (ctx->pin_free.size() >= 8) {  // keep the list short: drop the smallest
+        size_t small = 0;
+        for (size_t i = 1; i < ctx->pin_free.size(); ++i)
+            if (ctx->pin_free[i].second < ctx->pin_free[small].second) small = i;
+        if (ctx->pin_free[small].second < cap) {
+            cudaFreeHost(ctx->pin_free[small].first);
+            ctx->pin_free[small] = {p, cap};
+        } else {
+            cudaFreeHost(p);
+        }
+        return;
+    }
+    ctx->pin_free.emplace_back(p, cap);
 }
 
 extern "C" const char *vsk_last_error(const vsk_ctx *ctx) { return ctx ? ctx->err.c_str() : "no context"; }

@@ -44,6 +44,9 @@ struct vsk_ctx {
     int tiny_K = 0;
     uint8_t *d_tiny_dense = nullptr;  // [1024] composition id -> dense index
     uint8_t *d_tiny_ktab = nullptr;   // [K*K] distances between present ids
+    // page-locked host buffers handed out by vsk_pin_get and returned by vsk_pin_put (results of a
+    // run live in one until they are freed, so the buffer of one run serves the next)
+    std::vector<std::pair<void *, size_t>> pin_free;
     std::string err;
     uint64_t launches = 0;        // kernels launched through this context
     // optional per-launch timing of the DP kernel (bench.py's roofline leg)
@@ -67,6 +70,10 @@ struct vsk_profset {
 };
 
 int vsk_fail(vsk_ctx *ctx, int code, const char *fmt, ...);
+
+// page-locked host memory from the context's free list (nullptr when the allocation fails)
+void *vsk_pin_get(vsk_ctx *ctx, size_t bytes, size_t *cap);
+void vsk_pin_put(vsk_ctx *ctx, void *p, size_t cap);
 
 #define VSK_CUDA(ctx, call)                                                              \
     do {                                                                                 \

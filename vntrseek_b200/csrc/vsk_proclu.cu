@@ -19,6 +19,7 @@
 #include <cub/cub.cuh>
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "vsk_bits.cuh"
 #include "vsk_host.hpp"
@@ -62,6 +63,7 @@ struct vsk_reads {
     std::vector<void *> allocs;
     int64_t h2d_bytes = 0;
     vsk_idset present;  // composition ids that occur in this set
+    mutable bool checked = false;  // the pattern-size / tuple-size checks passed (done once per upload)
 };
 
 struct vsk_refs {
@@ -742,8 +744,14 @@ inline unsigned blocks(int64_t n, int per) { return (unsigned)((n + per - 1) / p
 }  // namespace
 
 struct vsk_proclu_result {
-    std::vector<vsk_link_rec> links;
+    // accepted links in a page-locked buffer of the context (vsk_pin_get), returned when the result is freed
+    vsk_ctx *ctx = nullptr;
+    vsk_link_rec *links = nullptr;
+    size_t n_links = 0, cap = 0;  // records, bytes
     vsk_proclu_stats stats;
+    ~vsk_proclu_result() {
+        if (links) vsk_pin_put(ctx, links, cap);
+    }
 };
 
 static int g_pool_set = 0;
@@ -775,7 +783,7 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, S.get(&d_stats, 12));
     VSK_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 12 * sizeof(unsigned long long), st));
     const int64_t nprof = p_end - p_begin;
-    vsk_stage_mark(ctx, nullptr);
+    vsk_stage_mark(ctx, "chunk_setup");
     vsk_seed_kernel<true><<<blocks(nprof * 32, 256), 256, 0, st>>>(reads, R->idx, R->luts, p_begin, p_end,
                                                                    nullptr, nullptr, d_off_emit, base, keys);
     ctx->launches++;
@@ -927,13 +935,23 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     if (hs[5])
         return vsk_fail(ctx, VSK_ERR_ABORT, "Edit_Distance_multiple_word_NoEndPenaltySeq1 returned -1. Aborting!");
     vsk_stage_mark(ctx, "flank_links");
-    const size_t old = out->links.size();
-    out->links.resize(old + (size_t)nl);
+    const size_t old = out->n_links;
+    if ((old + (size_t)nl) * sizeof(vsk_link_rec) > out->cap) {
+        size_t ncap = 0;
+        vsk_link_rec *nb = (vsk_link_rec *)vsk_pin_get(ctx, 2 * (old + (size_t)nl) * sizeof(vsk_link_rec), &ncap);
+        if (!nb) return vsk_fail(ctx, VSK_ERR_CUDA, "page-locked buffer for %zu links", old + (size_t)nl);
+        if (old) memcpy(nb, out->links, old * sizeof(vsk_link_rec));
+        if (out->links) vsk_pin_put(ctx, out->links, out->cap);
+        out->links = nb;
+        out->cap = ncap;
+    }
     if (nl)
-        VSK_CUDA(ctx, cudaMemcpyAsync(out->links.data() + old, recs2, sizeof(vsk_link_rec) * (size_t)nl,
+        VSK_CUDA(ctx, cudaMemcpyAsync(out->links + old, recs2, sizeof(vsk_link_rec) * (size_t)nl,
                                       cudaMemcpyDeviceToHost, st));
     VSK_CUDA(ctx, cudaStreamSynchronize(st));
+    out->n_links = old + (size_t)nl;
     out->stats.d2h_bytes += (int64_t)(sizeof(vsk_link_rec) * (size_t)nl);
+    vsk_stage_mark(ctx, "links_d2h");
     return VSK_OK;
 }
 
@@ -947,7 +965,7 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
     keep_pool(ctx);
     const vsk_trset *hq = Q->host;
     const vsk_seedinfo &si = vsk_seeds();
-    for (int32_t q = 0; q < hq->n; ++q) {  // the reference quits on these (psearch.c:784-787, hclust.h:866-869)
+    for (int32_t q = 0; q < hq->n && !Q->checked; ++q) {  // the reference quits on these (psearch.c:784-787, hclust.h:866-869)
         const int pmin = hq->patlen[(size_t)q];
         if (pmin < 7 || pmin > 5000) return vsk_fail(ctx, VSK_ERR_ABORT, "pmin(%d) must be in 7-5000 range!", pmin);
         if (!hq->master[(size_t)q]) continue;
@@ -959,7 +977,9 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
                                 si.tsize[t], (int)len);
         }
     }
+    Q->checked = true;
     vsk_proclu_result *res = new vsk_proclu_result();
+    res->ctx = ctx;
     memset(&res->stats, 0, sizeof res->stats);
     const int32_t nprof = 2 * Q->d.n;
     if (nprof == 0) { *out = res; return VSK_OK; }
@@ -987,9 +1007,18 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         S.get((uint8_t **)&tmp, tb);
         cub::DeviceScan::ExclusiveSum(tmp, tb, cnt, off, nprof + 1, st);
         vsk_stage_mark(ctx, "seed_count");
-        std::vector<int64_t> hoff((size_t)nprof + 1);
+        size_t hoff_cap = 0;
+        int64_t *hoff = (int64_t *)vsk_pin_get(ctx, sizeof(int64_t) * ((size_t)nprof + 1), &hoff_cap);
+        if (!hoff) {
+            delete res;
+            return vsk_fail(ctx, VSK_ERR_CUDA, "page-locked buffer for the key offsets");
+        }
+        struct PinGuard {
+            vsk_ctx *c; void *p; size_t cap;
+            ~PinGuard() { vsk_pin_put(c, p, cap); }
+        } hoff_guard{ctx, hoff, hoff_cap};
         unsigned long long hraw = 0;
-        cudaMemcpyAsync(hoff.data(), off, sizeof(int64_t) * ((size_t)nprof + 1), cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(hoff, off, sizeof(int64_t) * ((size_t)nprof + 1), cudaMemcpyDeviceToHost, st);
         cudaMemcpyAsync(&hraw, raw, sizeof hraw, cudaMemcpyDeviceToHost, st);
         e = cudaStreamSynchronize(st);
         if (e != cudaSuccess) {
@@ -1010,7 +1039,7 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         }
     }
     if (rc) { delete res; return rc; }
-    res->stats.confirmed = (uint64_t)res->links.size();
+    res->stats.confirmed = (uint64_t)res->n_links;
     *out = res;
     return VSK_OK;
 }
@@ -1030,8 +1059,8 @@ extern "C" int vsk_proclu_run(vsk_ctx *ctx, const vsk_refs *R, const vsk_trset *
 
 extern "C" int64_t vsk_proclu_result_links(const vsk_proclu_result *r, const vsk_link **links) {
     if (!r) return 0;
-    if (links) *links = reinterpret_cast<const vsk_link *>(r->links.data());
-    return (int64_t)r->links.size();
+    if (links) *links = reinterpret_cast<const vsk_link *>(r->links);
+    return (int64_t)r->n_links;
 }
 extern "C" void vsk_proclu_result_stats(const vsk_proclu_result *r, vsk_proclu_stats *s) {
     if (r && s) *s = r->stats;
