@@ -43,6 +43,29 @@ def test_psearch_matches_reference(tmp_path, dst_file, nref, nread, seed, maxlen
     assert canonical_clu(os.path.join(b, "reads.leb36.clu")) == canonical_clu(os.path.join(a, "reads.leb36.clu"))
 
 
+def test_psearch_very_long_patterns(tmp_path, dst_file, monkeypatch):
+    """patterns of 2100-4600 columns: more than 32 64-bit blocks in the LCS filter (several
+    systolic passes), several column strips and direction-word batches in the profile DP"""
+    if not _have_ref():
+        pytest.skip("oracle/_ref/psearch.exe not built")
+    from vntrseek_b200 import synth
+    orig = synth._pattern_length
+    monkeypatch.setattr(synth, "_pattern_length",
+                        lambda rng: int(rng.integers(2100, 4601)) if rng.random() < 0.25 else orig(rng))
+    a, b = str(tmp_path / "ref"), str(tmp_path / "our")
+    os.makedirs(a)
+    _make(a, 120, 160, 21, 5000)
+    shutil.copytree(a, b)
+    args = ["reference.leb36", "reads.leb36", dst_file, 88, 0, 50]
+    rc1, _, log1 = run(os.path.join(REF_BIN, "psearch.exe"), args, a)
+    rc2, _, log2 = run(os.path.join(OUR_BIN, "psearch.exe"), args, b)
+    assert rc1 == 0 and rc2 == 0, (rc1, rc2, log2[-500:])
+    c = parse_counters(log2)
+    assert c == parse_counters(log1)
+    assert c["ProfileAlignments"] > 0
+    assert canonical_clu(os.path.join(b, "reads.leb36.clu")) == canonical_clu(os.path.join(a, "reads.leb36.clu"))
+
+
 def test_psearch_golden_small(tmp_path, dst_file):
     """committed fixture (inputs + the reference's outputs), no reference binary needed"""
     from conftest import GOLDEN

@@ -17,6 +17,7 @@
 //   links    accepted (refkey, readkey, dir) records, in the order the reference
 //            would have called ClusterBaseAddLink, back to the host.
 #include <cub/cub.cuh>
+#include <thrust/iterator/transform_output_iterator.h>
 
 #include <algorithm>
 #include <cstdlib>
@@ -335,7 +336,8 @@ template <bool FILL>
 __global__ void __launch_bounds__(256)
 vsk_seed_kernel(DevTR reads, DevIndex idx, DevLuts luts, int32_t p_begin, int32_t p_end,
                 int64_t *__restrict__ cnt_emit, unsigned long long *__restrict__ raw_total,
-                const int64_t *__restrict__ off_emit, int64_t base, uint64_t *__restrict__ keys) {
+                const int64_t *__restrict__ off_emit, int64_t base, int key_shift,
+                uint64_t *__restrict__ keys) {
     const int lane = threadIdx.x & 31;
     const int32_t p = p_begin + (int32_t)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5);
     if (p >= p_end) return;
@@ -388,7 +390,8 @@ vsk_seed_kernel(DevTR reads, DevIndex idx, DevLuts luts, int32_t p_begin, int32_
                 }
                 int64_t dst = wbase + incl - nd;
                 if (found) {
-                    const uint64_t hi32 = (uint64_t)(uint32_t)p << 32;
+                    // sort key: read profile (relative to the chunk) above the reference profile
+                    const uint64_t hi32 = (uint64_t)(uint32_t)(p - p_begin) << key_shift;
                     for (int64_t k = w.s; k < w.e2; ++k) keys[dst++] = hi32 | (uint32_t)idx.e_prof[k];
                     if (w.extra) keys[dst] = hi32 | (uint32_t)idx.e_first[w.e2];
                 }
@@ -447,17 +450,25 @@ vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__r
             decided = true;
         }
     }
-    // more than one block: left to vsk_lcs_long_kernel (work queue), which keeps this kernel's warps
-    // uniform; one counter update per warp
+    // more than one block: left to vsk_lcs_sys_kernel, which keeps this kernel's warps uniform.  Three
+    // lists by the number of 64-column blocks W (2 / 3..8 / more), one counter update per warp each;
+    // list 1 grows from the back of the buffer list 0 grows from the front of
     const bool is_long = in_range && !decided && N > 64;
-    const unsigned lmask = __ballot_sync(0xffffffffu, is_long);
-    if (lmask) {
-        const int lane = threadIdx.x & 31, leader = __ffs(lmask) - 1;
+    const int W = (N + 63) >> 6;
+    const int cls = (W <= 2) ? 0 : (W <= 8) ? 1 : 2;
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const unsigned lmask = __ballot_sync(0xffffffffu, is_long && cls == c);
+        if (!lmask) continue;
+        const int leader = __ffs(lmask) - 1;
         unsigned base = 0;
-        if (lane == leader) base = atomicAdd(long_count, (unsigned)__popc(lmask));
+        if (lane == leader) base = atomicAdd(long_count + c, (unsigned)__popc(lmask));
         base = __shfl_sync(0xffffffffu, base, leader);
-        if (is_long) {
-            long_list[base + __popc(lmask & ((1u << lane) - 1u))] = (uint32_t)i;
+        if (is_long && cls == c) {
+            const int64_t k = (int64_t)base + __popc(lmask & ((1u << lane) - 1u));
+            const int64_t at = (c == 0) ? k : (c == 1) ? n - 1 - k : n + k;
+            long_list[at] = (uint32_t)i;
             flags[i] = 0;
         }
     }
@@ -479,72 +490,106 @@ vsk_lcs_filter_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__r
     flags[i] = (count >= luts.lcs_min[shortest]) ? 1 : 0;  // hclust.h:537-545
 }
 
-// The multi-block pairs deferred by vsk_lcs_filter_kernel.  Persistent threads; every lane pulls
-// its own next pair from a counter and the loop body is exactly one (block, row) step of the
-// recurrence, so lanes that are working on different pairs still execute the same instructions.
-// Word-outer / row-inner order with the inter-word carries kept one bit per row (as vsk_bits.cuh).
+// The multi-block pairs deferred by vsk_lcs_filter_kernel.  A group of G lanes works on one pair:
+// lane g owns block (64 columns) g of the bit vector and runs row s-g at step s, so the carry of
+// the row's addition moves one lane per step (shuffle) -- a systolic pass of M+G-1 steps; strings
+// of more than 64*G columns take several passes, the carries out of the last lane parked one bit
+// per row in shared memory (G = 32 only).  Persistent lanes with flattened state: the loop body is
+// one step, so groups that are at different places of different pairs execute the same
+// instructions; a group pulls its next pair from the list's counter when it is done.
+template <int G>
 __global__ void __launch_bounds__(128)
-vsk_lcs_long_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__restrict__ pairs,
-                    const uint32_t *__restrict__ long_list, const unsigned *__restrict__ long_count,
-                    unsigned *__restrict__ head, uint8_t *__restrict__ flags) {
-    const unsigned n = *long_count;
-    uint64_t carry[VSK_CW];
+vsk_lcs_sys_kernel(DevTR refs, DevTR reads, DevLuts luts, const uint64_t *__restrict__ pairs,
+                   const uint32_t *__restrict__ list, int list_dir, const unsigned *__restrict__ list_count,
+                   unsigned *__restrict__ head, uint8_t *__restrict__ flags) {
+    constexpr int NB = (G == 32) ? (VSK_MAXSTR / 64 + 2) : 1;
+    __shared__ uint64_t s_bnd[(G == 32) ? 4 : 1][2][NB];
+    const unsigned n = *list_count;
+    const int lane = threadIdx.x & 31, gl = lane & (G - 1);
+    const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (lane & ~(G - 1)));
+    uint64_t *bnd_in = s_bnd[(G == 32) ? (threadIdx.x >> 5) : 0][0], *bnd_out = s_bnd[(G == 32) ? (threadIdx.x >> 5) : 0][1];
     const uint64_t *planes = nullptr, *codes = nullptr;
-    uint64_t pl[4] = {0, 0, 0, 0}, V = 0, valid = 0, cw = 0, cin_w = 0, cout_w = 0;
-    int N = 0, M = 0, W = 0, j = 0, r = 0, count = 0, shortest = 0;
+    uint64_t pl[4] = {0, 0, 0, 0}, V = 0, valid = 0, cw = 0, cout_w = 0, bin_w = 0;
+    int N = 0, M = 0, W = 0, pass = 0, s = 0, count = 0, need = 0;
+    unsigned co_prev = 0;
     uint32_t item = 0;
     bool have = false;
     for (;;) {
         if (!have) {
-            const unsigned k = atomicAdd(head, 1u);
+            unsigned k = 0;
+            if (gl == 0) k = atomicAdd(head, 1u);
+            k = __shfl_sync(gmask, k, 0, G);
             if (k >= n) break;
-            item = long_list[k];
+            item = list[(int64_t)list_dir * (int64_t)k];
             const uint32_t p = (uint32_t)(pairs[item] >> 32), h = (uint32_t)pairs[item];
             const int nr = (int)(refs.cons_off[h + 1] - refs.cons_off[h]);
             const int mr = (int)(reads.cons_off[p + 1] - reads.cons_off[p]);
-            const bool ref_is_text = nr >= mr;
+            const bool ref_is_text = nr >= mr;  // on a tie string1 = the reference (multiple word.c:76-86)
             planes = ref_is_text ? refs.cons_planes + 4 * refs.cons_blk[h] : reads.cons_planes + 4 * reads.cons_blk[p];
             codes = ref_is_text ? reads.cons_codes + 2 * reads.cons_blk[p] : refs.cons_codes + 2 * refs.cons_blk[h];
             N = ref_is_text ? nr : mr;
             M = ref_is_text ? mr : nr;
-            shortest = M;
+            need = luts.lcs_min[M];  // hclust.h:537-545
             W = (N + 63) >> 6;
-            j = 0;
-            r = 0;
+            pass = 0;
+            s = 0;
             count = 0;
             have = true;
         }
-        if (r == 0) {  // start of a block
-#pragma unroll
-            for (int k = 0; k < 4; ++k) pl[k] = planes[4 * j + k];
+        if (s == 0) {  // start of a pass
+            const int j = pass * G + gl;
             const int top = N - j * 64;
-            valid = (top >= 64) ? ~0ull : ((1ull << top) - 1ull);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) pl[k] = (top > 0) ? planes[4 * j + k] : 0ull;
+            valid = (top >= 64) ? ~0ull : (top > 0) ? ((1ull << top) - 1ull) : 0ull;
             V = ~0ull;
+            co_prev = 0;
         }
-        if ((r & 31) == 0) cw = codes[r >> 5];
-        if ((r & 63) == 0) {
-            cin_w = (j > 0) ? carry[r >> 6] : 0ull;
-            cout_w = 0;
+        const int r = s - gl;
+        const unsigned cin_lane = __shfl_up_sync(gmask, co_prev, 1, G);
+        if (r >= 0 && r < M) {
+            if ((r & 31) == 0) cw = codes[r >> 5];
+            unsigned cin = cin_lane;
+            if (gl == 0) {
+                cin = 0;
+                if (G == 32 && pass > 0) {
+                    if ((r & 63) == 0) bin_w = bnd_in[r >> 6];
+                    cin = (unsigned)(bin_w >> (r & 63)) & 1u;
+                }
+            }
+            const uint64_t m = lcs_plane(pl, (uint32_t)(cw >> (2 * (r & 31))) & 3u) & valid;
+            const uint64_t x = V & m;
+            const uint64_t s1 = V + x;
+            unsigned co = (s1 < x) ? 1u : 0u;
+            const uint64_t s2 = s1 + cin;
+            co |= (s2 < s1) ? 1u : 0u;
+            V = s2 | (V & ~m);
+            co_prev = co;
+            if (G == 32 && gl == G - 1) {  // carries into the next pass, one bit per row
+                if ((r & 63) == 0) cout_w = 0;
+                cout_w |= (uint64_t)co << (r & 63);
+                if ((r & 63) == 63 || r == M - 1) bnd_out[r >> 6] = cout_w;
+            }
         }
-        const uint64_t m = lcs_plane(pl, (uint32_t)(cw >> (2 * (r & 31))) & 3u) & valid;
-        const uint64_t x = V & m;
-        const uint64_t s1 = V + x;
-        uint64_t co = (s1 < x) ? 1ull : 0ull;
-        const uint64_t s2 = s1 + ((cin_w >> (r & 63)) & 1ull);
-        co |= (s2 < s1) ? 1ull : 0ull;
-        V = s2 | (V & ~m);
-        cout_w |= co << (r & 63);
-        if ((r & 63) == 63 || r == M - 1) carry[r >> 6] = cout_w;
-        if (++r == M) {
-            count += __popcll(~V & valid);
-            r = 0;
-            ++j;
+        if (++s == M + G - 1) {  // end of the pass
+            int c = __popcll(~V & valid);
+#pragma unroll
+            for (int o = G >> 1; o > 0; o >>= 1) c += __shfl_xor_sync(gmask, c, o, G);
+            count += c;
+            ++pass;
+            s = 0;
             // the LCS length is the sum over blocks of the matched columns: stop as soon as the
             // threshold is reached, or cannot be reached even if every remaining column matched
-            const int need = luts.lcs_min[shortest], remaining = max(N - 64 * j, 0);
-            if (j == W || count >= need || count + remaining < need) {
-                flags[item] = (count >= need) ? 1 : 0;
+            const int remaining = max(N - 64 * G * pass, 0);
+            if (pass * G >= W || count >= need || count + remaining < need) {
+                if (gl == 0) flags[item] = (count >= need) ? 1 : 0;
                 have = false;
+            }
+            if (G == 32) {
+                __syncwarp();
+                uint64_t *t = bnd_in;
+                bnd_in = bnd_out;
+                bnd_out = t;
             }
         }
     }
@@ -754,6 +799,15 @@ struct vsk_proclu_result {
     }
 };
 
+struct WidenKey {  // chunk-relative sort key -> (read profile << 32) | reference profile
+    int shift;
+    uint32_t p_begin;
+    uint64_t mask;
+    __host__ __device__ uint64_t operator()(uint64_t k) const {
+        return ((uint64_t)((uint32_t)(k >> shift) + p_begin) << 32) | (k & mask);
+    }
+};
+
 static int g_pool_set = 0;
 
 // keep freed stream-ordered memory in the pool between runs
@@ -784,21 +838,27 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 12 * sizeof(unsigned long long), st));
     const int64_t nprof = p_end - p_begin;
     vsk_stage_mark(ctx, "chunk_setup");
+    // Sort keys are as narrow as the chunk allows (fewer radix passes): the read profile relative
+    // to the chunk above the reference profile; the unique pass widens them to (read << 32 | ref).
+    int key_shift = 1;
+    while (key_shift < 32 && ((uint64_t)(2 * (int64_t)refs.n - 1) >> key_shift)) ++key_shift;
+    int end_bit = key_shift + 1;
+    while (end_bit < 64 && ((uint64_t)(nprof - 1) >> (end_bit - key_shift))) ++end_bit;
     vsk_seed_kernel<true><<<blocks(nprof * 32, 256), 256, 0, st>>>(reads, R->idx, R->luts, p_begin, p_end,
-                                                                   nullptr, nullptr, d_off_emit, base, keys);
+                                                                   nullptr, nullptr, d_off_emit, base, key_shift, keys);
     ctx->launches++;
     vsk_stage_mark(ctx, "seed_fill");
     // candsort + dedup
-    int end_bit = 33;
-    while (end_bit < 64 && ((uint64_t)(uint32_t)p_end >> (end_bit - 32))) ++end_bit;
+    auto wide = thrust::make_transform_output_iterator(
+        keys, WidenKey{key_shift, (uint32_t)p_begin, ((uint64_t)1 << key_shift) - 1});
     size_t tb = 0, tb2 = 0;
     cub::DeviceRadixSort::SortKeys(nullptr, tb, keys, keys2, nkeys, 0, end_bit, st);
-    cub::DeviceSelect::Unique(nullptr, tb2, keys2, keys, d_n, nkeys, st);
+    cub::DeviceSelect::Unique(nullptr, tb2, keys2, wide, d_n, nkeys, st);
     tb = std::max(tb, tb2);
     void *tmp;
     VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb));
     VSK_CUDA(ctx, cub::DeviceRadixSort::SortKeys(tmp, tb, keys, keys2, nkeys, 0, end_bit, st));
-    VSK_CUDA(ctx, cub::DeviceSelect::Unique(tmp, tb, keys2, keys, d_n, nkeys, st));
+    VSK_CUDA(ctx, cub::DeviceSelect::Unique(tmp, tb, keys2, wide, d_n, nkeys, st));
     pairs = keys;
     vsk_stage_mark(ctx, "sort_unique");
     int64_t npairs = 0;
@@ -811,14 +871,21 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     VSK_CUDA(ctx, S.get(&flags, (size_t)npairs));
     uint32_t *long_list;
     unsigned *long_ctr;
-    VSK_CUDA(ctx, S.get(&long_list, (size_t)npairs));
-    VSK_CUDA(ctx, S.get(&long_ctr, 2));
-    VSK_CUDA(ctx, cudaMemsetAsync(long_ctr, 0, 2 * sizeof(unsigned), st));
+    VSK_CUDA(ctx, S.get(&long_list, 2 * (size_t)npairs));
+    VSK_CUDA(ctx, S.get(&long_ctr, 6));
+    VSK_CUDA(ctx, cudaMemsetAsync(long_ctr, 0, 6 * sizeof(unsigned), st));
     vsk_lcs_filter_kernel<<<blocks(npairs, 128), 128, 0, st>>>(refs, reads, R->luts, pairs, npairs, flags, long_list,
                                                               long_ctr);
-    vsk_lcs_long_kernel<<<(unsigned)ctx->sm_count * 8, 128, 0, st>>>(refs, reads, R->luts, pairs, long_list, long_ctr,
-                                                                    long_ctr + 1, flags);
+    // heaviest class first
+    vsk_lcs_sys_kernel<32><<<(unsigned)ctx->sm_count * 8, 128, 0, st>>>(refs, reads, R->luts, pairs, long_list + npairs, 1,
+                                                                       long_ctr + 2, long_ctr + 5, flags);
+    vsk_lcs_sys_kernel<8><<<(unsigned)ctx->sm_count * 8, 128, 0, st>>>(refs, reads, R->luts, pairs,
+                                                                      long_list + npairs - 1, -1, long_ctr + 1,
+                                                                      long_ctr + 4, flags);
+    vsk_lcs_sys_kernel<2><<<(unsigned)ctx->sm_count * 8, 128, 0, st>>>(refs, reads, R->luts, pairs, long_list, 1,
+                                                                      long_ctr, long_ctr + 3, flags);
     ctx->launches += 2;
+    ctx->launches += 4;
     pairs2 = keys2;
     size_t tb3 = 0;
     cub::DeviceSelect::Flagged(nullptr, tb3, pairs, flags, pairs2, d_n, npairs, st);
@@ -999,7 +1066,7 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         cudaMemsetAsync(raw, 0, sizeof(unsigned long long), st);
         cudaMemsetAsync(cnt + nprof, 0, sizeof(int64_t), st);
         vsk_seed_kernel<false><<<blocks((int64_t)nprof * 32, 256), 256, 0, st>>>(Q->d, R->idx, R->luts, 0, nprof, cnt,
-                                                                                raw, nullptr, 0, nullptr);
+                                                                                raw, nullptr, 0, 0, nullptr);
         ctx->launches++;
         size_t tb = 0;
         cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, off, nprof + 1, st);
