@@ -75,6 +75,39 @@ def test_dp_max_size_and_idempotence(ctx, oracle):
     ps.close()
 
 
+def test_dp_path_leaves_band(ctx, oracle):
+    """narrowband pairs whose unrestricted best path runs through the corners the band cuts off:
+    the direction-bit kernels must hand them to the cell-masking kernel (same answer as the oracle)"""
+    from vntrseek_b200 import synth
+    # Y: a nearly empty column (cheap to skip), X: a full one -- the best alignment skips the Y blocks
+    X, Y, Z = synth.comp_id(10, 0, 0, 0), synth.comp_id(0, 1, 0, 0), synth.comp_id(0, 0, 5, 5)
+    rng = np.random.default_rng(5)
+    profs, li, ti = [], [], []
+    for n, m in [(400, 200), (200, 100), (900, 500), (100, 60), (1500, 700), (300, 300)]:
+        left = np.array([Y] * n + [X] * m)
+        top = np.array([X] * m + [Y] * n)
+        profs += [left, top]
+        li.append(len(profs) - 2)
+        ti.append(len(profs) - 1)
+        # the same with noise, and a block that only fits far off the diagonal
+        l2 = left.copy()
+        l2[rng.integers(0, len(l2), len(l2) // 20)] = Z
+        t2 = np.concatenate([top[: m // 2], np.array([Z] * (n // 3)), top[m // 2:]])[: 2 * len(l2) - 1]
+        profs += [l2, t2]
+        li.append(len(profs) - 2)
+        ti.append(len(profs) - 1)
+    ps = ctx.profiles(profs)
+    got = ctx.pair_dp(ps, ps, li, ti, [1] * len(li), 88)
+    full = ctx.pair_dp(ps, ps, li, ti, [0] * len(li), 88)
+    differ = 0
+    for k in range(len(li)):
+        exp = oracle.dp(profs[li[k]], profs[ti[k]], 1, 88)
+        assert tuple(int(x) for x in got[k]) == exp, (k, len(profs[li[k]]), len(profs[ti[k]]))
+        differ += int(tuple(got[k]) != tuple(full[k]))
+    assert differ > 0  # the band did change some answers, i.e. the hand-back path ran
+    ps.close()
+
+
 def test_dp_empty_batch(ctx):
     ps = ctx.profiles([[1, 2, 3]])
     assert ctx.pair_dp(ps, ps, [], [], [], 88).shape == (0, 4)

@@ -4,6 +4,9 @@
 // GetFixedProfileAP / GetFixedProfileAPNarrowband do (reference src/psearch1.91/profile.h:2092-2210,
 // 1828-2009), except that the matrix holds 2-bit directions instead of 8-byte cells.
 //
+// (For narrowband pairs the sweep covers a superset of the band and the trace verifies that the path
+// stays inside it; see vsk_dp_trace_kernel.)
+//
 // Why: the one-kernel variant in vsk_dp.cu carries the two path sums with every cell, which is half
 // of its ~20 instructions per cell and three quarters of its per-lane state.  Dropping them lets a
 // lane own 16 columns (strips of 512) at fewer registers, i.e. fewer instructions per cell and less
@@ -29,11 +32,16 @@
 
 struct DdWarpSmem {
     uint8_t T[DD_TBYTES];   // compact substitution table [na][nb]
-    uint8_t mapL[1024];     // composition id -> local row index
     uint32_t bmL[32], bmT[32];
     uint16_t preT[32];
-    uint16_t invL[256], invT[256];
-    uint32_t ring[32][32];  // per-lane delay line of direction words, [row & 31][lane]
+    uint32_t win[64];       // sliding window of row records, slot = row & 63 (steady phase)
+    union {
+        struct {                 // while the pair is set up
+            uint8_t mapL[1024];  // composition id -> local row index
+            uint16_t invL[256], invT[256];
+        } su;
+        uint32_t ring[32][32];   // during the sweep: per-lane delay line of direction words, [row & 31][lane]
+    } u;
 };
 #define DD_SMEM_BYTES (2048 + DD_WARPS * sizeof(DdWarpSmem))
 
@@ -96,8 +104,8 @@ __device__ __forceinline__ bool dd_setup(const uint16_t *__restrict__ L, const u
         while (b) {
             const int id = lane * 32 + __ffs(b) - 1;
             b &= b - 1;
-            ws.mapL[id] = (uint8_t)rk;
-            ws.invL[rk] = (uint16_t)id;
+            ws.u.su.mapL[id] = (uint8_t)rk;
+            ws.u.su.invL[rk] = (uint16_t)id;
             ++rk;
         }
         b = bt;
@@ -105,29 +113,29 @@ __device__ __forceinline__ bool dd_setup(const uint16_t *__restrict__ L, const u
         while (b) {
             const int id = lane * 32 + __ffs(b) - 1;
             b &= b - 1;
-            ws.invT[rk] = (uint16_t)id;
+            ws.u.su.invT[rk] = (uint16_t)id;
             ++rk;
         }
         __syncwarp();
 #pragma unroll 4
         for (int a = 0; a < na; ++a) {
-            const uint8_t *drow = dist + (int)ws.invL[a] * VSK_DROW;
-            for (int c = lane; c < nb; c += 32) ws.T[a * nb + c] = __ldg(drow + ws.invT[c]);
+            const uint8_t *drow = dist + (int)ws.u.su.invL[a] * VSK_DROW;
+            for (int c = lane; c < nb; c += 32) ws.T[a * nb + c] = __ldg(drow + ws.u.su.invT[c]);
         }
         __syncwarp();
     }
     for (int i = lane; i < l1; i += 32) {
         const int id = L[i];
-        rowrec[i] = dd_pack_row(smemt ? (int)ws.mapL[id] * nb : id, s_gapnd[id]);
+        rowrec[i] = dd_pack_row(smemt ? (int)ws.u.su.mapL[id] * nb : id, s_gapnd[id]);
     }
     __syncwarp();
     nb_out = nb;
     return smemt;
 }
 
-template <int CPL, bool MASKED, bool SMEMT>
+template <int CPL, bool SMEMT>
 __device__ __forceinline__ uint32_t dd_row_cells(int (&Hd)[CPL], const int (&tb)[CPL], const int (&gt)[CPL], int dgd,
-                                                 int lfd, const uint8_t *__restrict__ trow, int gl, int lo, int hi) {
+                                                 int lfd, const uint8_t *__restrict__ trow, int gl) {
     uint32_t w = 0;
 #pragma unroll
     for (int j = 0; j < CPL; ++j) {
@@ -138,12 +146,9 @@ __device__ __forceinline__ uint32_t dd_row_cells(int (&Hd)[CPL], const int (&tb)
         const int e = lfd + gt[j];  // right
         // min3switch (profile.h:1098-1099): diag if sa<=f && sa<=e; else down if f<=e; else right.
         // d = min3, so "not diagonal" is the sign of d - sa and "right" is the sign of e - f.
-        int d = min(min(sa, f), e);
+        const int d = min(min(sa, f), e);
         w = __funnelshift_l((uint32_t)(d - sa), w, 1);
         w = __funnelshift_l((uint32_t)(e - f), w, 1);
-        if (MASKED) {
-            if (j < lo || j > hi) d = VSK_BIG;
-        }
         dgd = upd;
         Hd[j] = d;
         lfd = d;
@@ -227,10 +232,8 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             const bool active = !check || ((r >= r_lo) && (r < r_hi));
             const uint32_t rec = rec_next;
             rec_next = __ldcg(rowrec + min(max(r + 1, 0), l1 - 1));
-            const int gl = (rec >> 16) & 255;
+            const int gl = (int)(rec >> 16);
             const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
-            int lo = 0, hi = CPL;
-            bool need_mask = false;
             if (active) {
                 if (lane == 0) {
                     if (pass == 0) {
@@ -240,30 +243,66 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                         nxt = (r + 1 < prev_r_hi) ? __ldcg(bscr + r + 1) : VSK_BIG;
                     }
                 }
-                if (banded) {  // profile.h:1835-1839
-                    const int center = __double2int_rz(__dmul_rn((double)(r + 1), sv));
-                    lo = max(1, center - br) - (cbase + 1);
-                    hi = min(l2, center + br) - (cbase + 1);
-                    need_mask = (lo > 0) || (hi < CPL - 1);
-                }
-            }
-            const bool anymask = banded && __any_sync(DD_FULL, need_mask);
-            if (active) {
-                uint32_t w;
-                if (anymask) w = dd_row_cells<CPL, true, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl, lo, hi);
-                else w = dd_row_cells<CPL, false, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl, lo, hi);
+                const uint32_t w = dd_row_cells<CPL, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl);
                 dgd = lfd;
-                ws.ring[r & 31][lane] = w;
+                ws.u.ring[r & 31][lane] = w;
                 if (wr_scratch) bscr[r] = Hd[CPL - 1];
             }
             // every lane's word of row s-31 is in its delay line now: one 128-byte line goes out
             const int ro = s - 31;
-            if (ro >= r_lo && ro < r_hi) dstrip[(size_t)ro * 32] = ws.ring[ro & 31][lane];
+            if (ro >= r_lo && ro < r_hi) dstrip[(size_t)ro * 32] = ws.u.ring[ro & 31][lane];
         };
         const int s_fill_end = min(r_lo + 31, r_hi + 31);
         int s = r_lo;
         for (; s < s_fill_end; ++s) step(s, true);
-        for (; s < r_hi; ++s) step(s, false);
+        if (s < r_hi) {
+            // steady phase: every lane has a row in [r_lo, r_hi) and every step sends a row out; the
+            // addresses advance by one row per step (the scratch has a row of slack past l1)
+            int *bp = bscr + (s - lane);                   // lane 31 leaves its row's last cell here
+            uint32_t *dp = dstrip + (size_t)(s - 31) * 32; // row s-31 goes out
+            // Row records come through a 64-row window in shared memory and the left neighbours of
+            // lane 0 through a register per lane, both fetched a block of 32 steps ahead, so that no
+            // step waits for global memory.
+            __syncwarp();
+            ws.win[(s - 31 + lane) & 63] = __ldcg(rowrec + s - 31 + lane);
+            ws.win[(s + 1 + lane) & 63] = __ldcg(rowrec + s + 1 + lane);
+            int bcur = (pass > 0) ? __ldcg(bscr + s + 1 + lane) : 0, bpre = 0;
+            uint32_t wpre = 0;
+            __syncwarp();
+            rec_next = ws.win[(s - lane) & 63];
+            for (int k = 0; s < r_hi; ++s, ++k) {
+                const int r = s - lane;
+                if ((k & 31) == 0) {  // rows s+33 .. s+64: needed from step s+32 on
+                    wpre = __ldcg(rowrec + s + 33 + lane);
+                    if (pass > 0) bpre = __ldcg(bscr + s + 33 + lane);
+                }
+                int lfd = __shfl_up_sync(DD_FULL, Hd[CPL - 1], 1);
+                const uint32_t rec = rec_next;
+                rec_next = ws.win[(r + 1) & 63];
+                const int gl = (int)(rec >> 16);
+                const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
+                if (pass == 0) {
+                    if (lane == 0) lfd = dgd + gl;  // column 0, profile.h:2084-2090
+                } else {
+                    const int v = __shfl_sync(DD_FULL, bcur, k & 31);  // previous strip's last cell of row s+1
+                    if (lane == 0) lfd = nxt;
+                    nxt = (s + 1 < prev_r_hi) ? v : VSK_BIG;
+                }
+                const uint32_t w = dd_row_cells<CPL, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl);
+                dgd = lfd;
+                ws.u.ring[r & 31][lane] = w;
+                if (wr_scratch) *bp = Hd[CPL - 1];
+                ++bp;
+                *dp = ws.u.ring[(s + 1) & 31][lane];
+                dp += 32;
+                if ((k & 31) == 31) {  // rows <= s-31 are done with: their slots take rows s+2 .. s+33
+                    __syncwarp();
+                    ws.win[(s + 2 + lane) & 63] = wpre;
+                    bcur = bpre;
+                    __syncwarp();
+                }
+            }
+        }
         for (; s < r_hi + 31; ++s) step(s, true);
         prev_r_hi = r_hi;
         __syncwarp();
@@ -322,10 +361,18 @@ vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restr
 }
 
 // Trace: one thread per pair walks the stored directions from (l1,l2) to (0,0) and sums what the
-// reference's traceback sums (profile.h:2135-2210): dashnum*cost, dashnum, path length.  Pairs whose
-// corner is unreachable (distance >= BIG: the band is disconnected) are handed back on `redo`; the
-// one-kernel variant defines their result.
+// reference's traceback sums (profile.h:2135-2210): dashnum*cost, dashnum, path length.
+//
+// Narrowband pairs: the forward sweep does not mask the cells outside the band (it only skips the
+// rows of a strip the band cannot touch and closes row 0 past column br), i.e. it solves the DP on a
+// region that contains the band.  If the path it finds stays inside the band, the banded DP finds
+// the same path with the same values: restricting the region can only raise the value of a
+// candidate that is off the path, and min3switch's preference order (diagonal, down, right) then
+// picks the same candidate.  The trace checks every cell of the path against the band; a pair whose
+// path leaves it -- or whose corner is unreachable (distance >= BIG) -- is handed back on `redo`
+// and goes through vsk_dp_kernel, which masks cell by cell.
 #define DT_THREADS 128
+#define DT_AHEAD 12
 
 __global__ void __launch_bounds__(DT_THREADS)
 vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
@@ -357,8 +404,29 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
         int sl = (c - 1) / cpl, j = (c - 1) - sl * cpl;
         uint32_t w = 0;
         int wr = -1, wl = -1;  // (row, strip*32+lane) of the cached word
+        const bool banded = job.br >= 0;
+        int blo = 1, bhi = job.l2;  // in-band columns of row r (profile.h:1835-1839)
+        bool off_band = false;
         while (r > 0 && c > 0) {
+            if (wr != r) {
+                if (banded) {
+                    const int center = __double2int_rz(__dmul_rn((double)r, job.svector));
+                    blo = max(1, center - job.br);
+                    bhi = min(job.l2, center + job.br);
+                }
+            }
+            if (c < blo || c > bhi) {
+                off_band = true;
+                break;
+            }
             if (wr != r || wl != sl) {
+                if (wr != r && r > DT_AHEAD) {
+                    // the path runs roughly diagonally: pull the 32-byte sector (8 lanes' words) it
+                    // will most likely need DT_AHEAD rows from now into L2 while this row's word is in flight
+                    const int pc = max(c - 1 - DT_AHEAD, 0) / cpl;
+                    const uint32_t *pp = dir + ((size_t)(pc >> 5) * l1 + (r - 1 - DT_AHEAD)) * 32 + (pc & 31);
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pp));
+                }
                 w = __ldcs(dir + ((size_t)(sl >> 5) * l1 + (r - 1)) * 32 + (sl & 31));
                 wr = r;
                 wl = sl;
@@ -391,6 +459,10 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
                 }
             }
             ++len;
+        }
+        if (off_band || (banded && r == 0 && c > job.br)) {  // row 0 is open up to column br (profile.h:1801-1802)
+            redo[atomicAdd(redo_count, 1)] = job;
+            continue;
         }
         for (; r > 0; --r, ++len) {  // column 0: gaps in the top profile
             const int gnl = s_gapnd[L[r - 1]];
@@ -497,12 +569,13 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
                                            (int)DD_SMEM_BYTES));
         g_dd_attr_set = 1;
     }
+    const size_t dd_smem = DD_SMEM_BYTES;
     int per_sm = 0;
     VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_dir_kernel, DD_WARPS * 32,
-                                                                 DD_SMEM_BYTES));
+                                                                 dd_smem));
     if (per_sm < 1) per_sm = 1;
     const int grid = ctx->sm_count * per_sm;
-    const int stride = ((max_l1 + 31) / 32) * 32;
+    const int stride = ((max_l1 + 31) / 32) * 32 + 128;  // slack: the steady phase fetches up to 96 rows past the last
     const size_t scr_ints = (size_t)grid * DD_WARPS * 2 * stride;
 
     uint32_t *d_dir = nullptr;
@@ -524,7 +597,7 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
         cudaStream_t st = (b & 1) ? s1 : s0;
         uint32_t *dir = d_dir + (size_t)(b & 1) * half_words;
         int *scr = d_scr + (size_t)(b & 1) * scr_ints;
-        vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, DD_SMEM_BYTES, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
+        vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, dd_smem, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
                                                                       batch_words, ctx->d_dist, ctx->d_gapnd, scr,
                                                                       stride, dir, d_queue, d_out);
         vsk_dp_trace_kernel<<<ctx->sm_count * 8, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
