@@ -114,6 +114,7 @@ extern "C" void vsk_destroy(vsk_ctx *ctx) {
     for (int i = 0; i < 4; ++i)
         if (ctx->dd_ev[i]) cudaEventDestroy(ctx->dd_ev[i]);
     for (auto &b : ctx->pin_free) cudaFreeHost(b.first);
+    for (void *m : ctx->dd_mem) cudaFree(m);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

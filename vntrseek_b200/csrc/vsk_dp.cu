@@ -716,8 +716,6 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
                 ctx->d_queue, d_out, d_redo_n, 0);
             ctx->launches++;
             VSK_CUDA(ctx, cudaGetLastError());
-            VSK_CUDA(ctx, cudaFreeAsync(d_redo, ctx->stream));
-            VSK_CUDA(ctx, cudaFreeAsync(d_redo_n, ctx->stream));
         }
     }
     if (ctx->profile) {

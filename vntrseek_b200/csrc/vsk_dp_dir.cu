@@ -14,9 +14,11 @@
 //
 // Direction words: one uint32 per (row, lane) of a strip = the CPL (8, 12 or 16, chosen per pair by
 // dd_plan so that the strips fit the pair) cells of that lane; cell j holds "not diagonal" in bit
-// 2(CPL-1-j)+1 and "right rather than down" in bit 2(CPL-1-j).  A lane finishes row R at step R+lane; it
-// parks the word in a private shared-memory delay line and every lane stores its word of row R at
-// step R+31, so the 32 words of a row go out as one 128-byte line.
+// 2(CPL-1-j)+1 and "right rather than down" in bit 2(CPL-1-j).  They are stored lane-major: the words
+// of one lane (strip*32 + lane) for rows 0..l1-1 are contiguous (padded to 8 rows), because that is
+// how the trace reads them -- a path stays in one lane's columns for about CPL rows, so eight of its
+// steps share a 32-byte sector.  A lane parks its words in a 16-row ring in shared memory and every
+// eighth step all lanes store their last complete group of 8 rows as one sector.
 #include <algorithm>
 #include <cstdlib>
 
@@ -40,7 +42,7 @@ struct DdWarpSmem {
             uint8_t mapL[1024];  // composition id -> local row index
             uint16_t invL[256], invT[256];
         } su;
-        uint32_t ring[32][32];   // during the sweep: per-lane delay line of direction words, [row & 31][lane]
+        uint32_t ring[32][16];   // during the sweep: the last 16 direction words of each lane, [lane][row & 15]
     } u;
 };
 #define DD_SMEM_BYTES (2048 + DD_WARPS * sizeof(DdWarpSmem))
@@ -156,6 +158,15 @@ __device__ __forceinline__ uint32_t dd_row_cells(int (&Hd)[CPL], const int (&tb)
     return w;
 }
 
+// stores rows g0..g0+7 (g0 a multiple of 8) of this lane's ring as one 32-byte sector
+__device__ __forceinline__ void dd_flush8(const DdWarpSmem &ws, int lane, uint32_t *__restrict__ dlane, int g0) {
+    const uint4 a = *reinterpret_cast<const uint4 *>(&ws.u.ring[lane][g0 & 15]);
+    const uint4 b = *reinterpret_cast<const uint4 *>(&ws.u.ring[lane][(g0 & 15) + 4]);
+    uint4 *dst = reinterpret_cast<uint4 *>(dlane + g0);
+    __stcs(dst, a);
+    __stcs(dst + 1, b);
+}
+
 template <int CPL, bool SMEMT>
 __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *__restrict__ Tp,
                                         const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
@@ -224,7 +235,9 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
         int nxt = VSK_BIG;
         if (rd_scratch && r_lo < prev_r_hi) nxt = __ldcg(bscr + r_lo);
         uint32_t rec_next = __ldcg(rowrec + min(max(r_lo - lane, 0), l1 - 1));
-        uint32_t *dstrip = dir + (size_t)pass * l1 * 32 + lane;
+        const int l1p = (l1 + 7) & ~7;
+        uint32_t *dlane = dir + (size_t)(pass * 32 + lane) * l1p;  // this lane's words, row-indexed
+        const int g_lo = r_lo & ~7;
 
         auto step = [&](const int s, const bool check) {
             const int r = s - lane;
@@ -245,12 +258,13 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                 }
                 const uint32_t w = dd_row_cells<CPL, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl);
                 dgd = lfd;
-                ws.u.ring[r & 31][lane] = w;
+                ws.u.ring[lane][r & 15] = w;
                 if (wr_scratch) bscr[r] = Hd[CPL - 1];
             }
-            // every lane's word of row s-31 is in its delay line now: one 128-byte line goes out
-            const int ro = s - 31;
-            if (ro >= r_lo && ro < r_hi) dstrip[(size_t)ro * 32] = ws.u.ring[ro & 31][lane];
+            if ((s & 7) == 7) {  // the lane's last complete group of 8 rows goes out
+                const int g0 = ((min(r, r_hi - 1) + 1) & ~7) - 8;
+                if (g0 >= g_lo) dd_flush8(ws, lane, dlane, g0);
+            }
         };
         const int s_fill_end = min(r_lo + 31, r_hi + 31);
         int s = r_lo;
@@ -259,7 +273,6 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             // steady phase: every lane has a row in [r_lo, r_hi) and every step sends a row out; the
             // addresses advance by one row per step (the scratch has a row of slack past l1)
             int *bp = bscr + (s - lane);                   // lane 31 leaves its row's last cell here
-            uint32_t *dp = dstrip + (size_t)(s - 31) * 32; // row s-31 goes out
             // Row records come through a 64-row window in shared memory and the left neighbours of
             // lane 0 through a register per lane, both fetched a block of 32 steps ahead, so that no
             // step waits for global memory.
@@ -290,11 +303,13 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                 }
                 const uint32_t w = dd_row_cells<CPL, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl);
                 dgd = lfd;
-                ws.u.ring[r & 31][lane] = w;
+                ws.u.ring[lane][r & 15] = w;
                 if (wr_scratch) *bp = Hd[CPL - 1];
                 ++bp;
-                *dp = ws.u.ring[(s + 1) & 31][lane];
-                dp += 32;
+                if ((s & 7) == 7) {  // the lane's last complete group of 8 rows goes out
+                    const int g0 = ((r + 1) & ~7) - 8;
+                    if (g0 >= g_lo) dd_flush8(ws, lane, dlane, g0);
+                }
                 if ((k & 31) == 31) {  // rows <= s-31 are done with: their slots take rows s+2 .. s+33
                     __syncwarp();
                     ws.win[(s + 2 + lane) & 63] = wpre;
@@ -304,6 +319,11 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             }
         }
         for (; s < r_hi + 31; ++s) step(s, true);
+        if (r_hi > r_lo) {  // the rows after the last complete group (and that group once more)
+            const int ga = (r_hi - 1) & ~7;
+            if (ga - 8 >= g_lo) dd_flush8(ws, lane, dlane, ga - 8);
+            dd_flush8(ws, lane, dlane, ga);
+        }
         prev_r_hi = r_hi;
         __syncwarp();
     }
@@ -372,7 +392,7 @@ vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restr
 // path leaves it -- or whose corner is unreachable (distance >= BIG) -- is handed back on `redo`
 // and goes through vsk_dp_kernel, which masks cell by cell.
 #define DT_THREADS 128
-#define DT_AHEAD 12
+#define DT_AHEAD 24
 
 __global__ void __launch_bounds__(DT_THREADS)
 vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
@@ -395,7 +415,7 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
         const uint16_t *L = left_ids + job.left_off;
         const uint16_t *Tp = top_ids + job.top_off;
         const uint32_t *dir = dirbuf + (dir_off[ji] - (int64_t)batch * batch_words);
-        const int l1 = job.l1;
+        const int l1p = (job.l1 + 7) & ~7;
         int cpl, ns;
         dd_plan(job.l1, job.l2, cpl, ns);
         int r = job.l1, c = job.l2;
@@ -420,14 +440,18 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
                 break;
             }
             if (wr != r || wl != sl) {
-                if (wr != r && r > DT_AHEAD) {
-                    // the path runs roughly diagonally: pull the 32-byte sector (8 lanes' words) it
-                    // will most likely need DT_AHEAD rows from now into L2 while this row's word is in flight
-                    const int pc = max(c - 1 - DT_AHEAD, 0) / cpl;
-                    const uint32_t *pp = dir + ((size_t)(pc >> 5) * l1 + (r - 1 - DT_AHEAD)) * 32 + (pc & 31);
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pp));
+                const uint32_t *wp = dir + (size_t)sl * l1p + (r - 1);
+                if (((r - 1) & 7) == 7 || wl != sl) {
+                    // entering a new 32-byte sector (8 rows of one lane): the path runs roughly
+                    // diagonally, so pull the sector it will most likely need DT_AHEAD rows from now
+                    // into L2 while this one is in flight
+                    const int pr = r - 1 - DT_AHEAD;
+                    if (pr >= 0) {
+                        const int pc = max(c - 1 - DT_AHEAD, 0) / cpl;
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(dir + (size_t)pc * l1p + pr));
+                    }
                 }
-                w = __ldcs(dir + ((size_t)(sl >> 5) * l1 + (r - 1)) * 32 + (sl & 31));
+                w = __ldg(wp);
                 wr = r;
                 wl = sl;
             }
@@ -485,7 +509,7 @@ __global__ void vsk_dd_words_kernel(const vsk_dp_job *__restrict__ jobs, int n, 
     const int l1 = jobs[i].l1, l2 = jobs[i].l2;
     int cpl, ns;
     dd_plan(l1, l2, cpl, ns);
-    words[i] = VSK_DP_DIRJOB(l2) ? (int64_t)ns * l1 * 32 : 0;
+    words[i] = VSK_DP_DIRJOB(l2) ? (int64_t)ns * 32 * ((l1 + 7) & ~7) : 0;
 }
 
 // bounds[b] = first job whose direction words start at or after b*batch_words (jobs of a batch are
@@ -519,47 +543,62 @@ int vsk_dp_dir_begin(vsk_ctx *ctx) {
     return VSK_OK;
 }
 
+// grow-only buffer k of the context
+static int dd_reserve(vsk_ctx *ctx, int k, size_t bytes, void **out) {
+    if (bytes > ctx->dd_cap[k]) {
+        if (ctx->dd_mem[k]) VSK_CUDA(ctx, cudaFree(ctx->dd_mem[k]));  // waits for the device
+        ctx->dd_mem[k] = nullptr;
+        ctx->dd_cap[k] = 0;
+        const size_t want = bytes + bytes / 8 + 256;
+        VSK_CUDA(ctx, cudaMalloc(&ctx->dd_mem[k], want));
+        ctx->dd_cap[k] = want;
+    }
+    *out = ctx->dd_mem[k];
+    return VSK_OK;
+}
+
 // Runs the jobs of d_jobs[0..n) that satisfy VSK_DP_DIRJOB through the two kernels above, in batches
 // whose direction words fit the buffer; the batches alternate between two side streams (each with
 // its own half of the buffer) that fork from the vsk_dp_dir_begin mark and join ctx->stream at the
-// end.  *redo / *redo_count (device, stream-ordered allocations the caller frees on ctx->stream)
-// receive the pairs that must go through vsk_dp_kernel; both stay null when no job qualified.
+// end.  *redo / *redo_count (device, owned by the context) receive the pairs that must go through
+// vsk_dp_kernel; both stay null when no job qualified.
 int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids, const vsk_dp_job *d_jobs,
                       int64_t n, int32_t max_l1, int4 *d_out, vsk_dp_job **redo, int **redo_count) {
     *redo = nullptr;
     *redo_count = nullptr;
     if (n <= 0) return VSK_OK;
     cudaStream_t s0 = ctx->dd_stream[0], s1 = ctx->dd_stream[1];
-    VSK_CUDA(ctx, cudaStreamWaitEvent(s0, ctx->dd_ev[0], 0));
+    int rc;
     int64_t *d_words = nullptr, *d_off = nullptr;
-    VSK_CUDA(ctx, cudaMallocAsync(&d_words, (size_t)(n + 1) * sizeof(int64_t), s0));
-    VSK_CUDA(ctx, cudaMallocAsync(&d_off, (size_t)(n + 1) * sizeof(int64_t), s0));
+    void *d_tmp = nullptr;
+    size_t tmp_bytes = 0;
+    VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
+    if ((rc = dd_reserve(ctx, 0, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_words))) return rc;
+    if ((rc = dd_reserve(ctx, 1, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_off))) return rc;
+    if ((rc = dd_reserve(ctx, 2, tmp_bytes + 16, &d_tmp))) return rc;
+    VSK_CUDA(ctx, cudaStreamWaitEvent(s0, ctx->dd_ev[0], 0));
     VSK_CUDA(ctx, cudaMemsetAsync(d_words + n, 0, sizeof(int64_t), s0));
     vsk_dd_words_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s0>>>(d_jobs, (int)n, d_words);
     ctx->launches++;
-    size_t tmp_bytes = 0;
-    VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
-    void *d_tmp = nullptr;
-    VSK_CUDA(ctx, cudaMallocAsync(&d_tmp, tmp_bytes ? tmp_bytes : 16, s0));
     VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
     ctx->launches += 2;
     int64_t total = 0;
     VSK_CUDA(ctx, cudaMemcpyAsync(&total, d_off + n, sizeof(int64_t), cudaMemcpyDeviceToHost, s0));
     VSK_CUDA(ctx, cudaStreamSynchronize(s0));
-    VSK_CUDA(ctx, cudaFreeAsync(d_tmp, s0));
-    VSK_CUDA(ctx, cudaFreeAsync(d_words, s0));
     if (total == 0) {
-        VSK_CUDA(ctx, cudaFreeAsync(d_off, s0));
+        VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[2], s0));
+        VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[2], 0));
         return VSK_OK;
     }
-    // batch size: VSK_DIR_BATCH_MB of direction words per stream (default 4 GiB), at most a sixth of the free memory
+    // batch size: VSK_DIR_BATCH_MB of direction words per stream (default 4 GiB), at most a sixth of the
+    // memory that is free or already ours
     int64_t batch_mb = 4096;
     if (const char *e = getenv("VSK_DIR_BATCH_MB")) batch_mb = std::max<int64_t>(16, atoll(e));
     size_t free_b = 0, total_b = 0;
     VSK_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
-    const int64_t max_job_words = (int64_t)((VSK_MAXPROF + 255) / 256) * max_l1 * 32;  // strips are >= 256 columns
-    int64_t batch_words = std::min<int64_t>(batch_mb << 18, (int64_t)(free_b / 6 / 4));
-    batch_words = std::max<int64_t>(batch_words, max_job_words);
+    const int64_t max_job_words = (int64_t)((VSK_MAXPROF + 255) / 256) * ((max_l1 + 7) & ~7) * 32;  // strips are >= 256 columns
+    int64_t batch_words = std::min<int64_t>(batch_mb << 18, (int64_t)((free_b + ctx->dd_cap[3]) / 6 / 4));
+    batch_words = std::max<int64_t>(batch_words & ~(int64_t)7, max_job_words);
     const int nb = (int)((total + batch_words - 1) / batch_words);
     const int64_t half_words = (nb == 1) ? total : batch_words + max_job_words;
     const int nhalf = nb == 1 ? 1 : 2;
@@ -579,27 +618,26 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     const size_t scr_ints = (size_t)grid * DD_WARPS * 2 * stride;
 
     uint32_t *d_dir = nullptr;
-    int *d_bounds = nullptr, *d_queue = nullptr, *d_scr = nullptr;
-    VSK_CUDA(ctx, cudaMallocAsync(&d_dir, (size_t)half_words * nhalf * 4, s0));
-    VSK_CUDA(ctx, cudaMallocAsync(&d_bounds, (size_t)(nb + 1) * sizeof(int), s0));
-    VSK_CUDA(ctx, cudaMallocAsync(&d_queue, (size_t)(nb + 1) * sizeof(int), s0));
-    VSK_CUDA(ctx, cudaMallocAsync(&d_scr, scr_ints * nhalf * sizeof(int), s0));
-    VSK_CUDA(ctx, cudaMallocAsync(redo, (size_t)n * sizeof(vsk_dp_job), s0));
-    VSK_CUDA(ctx, cudaMallocAsync(redo_count, sizeof(int), s0));
-    VSK_CUDA(ctx, cudaMemsetAsync(d_queue, 0, (size_t)(nb + 1) * sizeof(int), s0));
-    VSK_CUDA(ctx, cudaMemsetAsync(*redo_count, 0, sizeof(int), s0));
+    int *d_small = nullptr, *d_scr = nullptr;
+    if ((rc = dd_reserve(ctx, 3, (size_t)half_words * nhalf * 4, (void **)&d_dir))) return rc;
+    if ((rc = dd_reserve(ctx, 4, scr_ints * 2 * sizeof(int), (void **)&d_scr))) return rc;
+    if ((rc = dd_reserve(ctx, 5, (size_t)(2 * (nb + 1) + 1) * sizeof(int), (void **)&d_small))) return rc;
+    if ((rc = dd_reserve(ctx, 6, (size_t)n * sizeof(vsk_dp_job), (void **)redo))) return rc;
+    int *d_bounds = d_small, *d_queue = d_small + (nb + 1);
+    *redo_count = d_small + 2 * (nb + 1);
+    VSK_CUDA(ctx, cudaMemsetAsync(d_queue, 0, (size_t)(nb + 2) * sizeof(int), s0));  // queue heads + redo count
     vsk_dd_bounds_kernel<<<(nb + 1 + 127) / 128, 128, 0, s0>>>(d_off, (int)n, batch_words, nb, d_bounds);
     ctx->launches++;
     VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[1], s0));
-    VSK_CUDA(ctx, cudaStreamWaitEvent(s1, ctx->dd_ev[1], 0));  // s1 starts after the buffers exist
+    VSK_CUDA(ctx, cudaStreamWaitEvent(s1, ctx->dd_ev[1], 0));  // s1 starts after the batch bounds exist
 
     for (int b = 0; b < nb; ++b) {
         cudaStream_t st = (b & 1) ? s1 : s0;
         uint32_t *dir = d_dir + (size_t)(b & 1) * half_words;
         int *scr = d_scr + (size_t)(b & 1) * scr_ints;
         vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, dd_smem, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
-                                                                      batch_words, ctx->d_dist, ctx->d_gapnd, scr,
-                                                                      stride, dir, d_queue, d_out);
+                                                                batch_words, ctx->d_dist, ctx->d_gapnd, scr, stride, dir,
+                                                                d_queue, d_out);
         vsk_dp_trace_kernel<<<ctx->sm_count * 8, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
                                                                        batch_words, ctx->d_dist, ctx->d_gapnd, dir,
                                                                        d_out, *redo, *redo_count);
@@ -611,10 +649,5 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[3], s1));
     VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[2], 0));
     VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[3], 0));
-    VSK_CUDA(ctx, cudaFreeAsync(d_scr, ctx->stream));
-    VSK_CUDA(ctx, cudaFreeAsync(d_dir, ctx->stream));
-    VSK_CUDA(ctx, cudaFreeAsync(d_bounds, ctx->stream));
-    VSK_CUDA(ctx, cudaFreeAsync(d_queue, ctx->stream));
-    VSK_CUDA(ctx, cudaFreeAsync(d_off, ctx->stream));
     return VSK_OK;
 }

@@ -37,6 +37,10 @@ struct vsk_ctx {
     // one forward sweep is filled by the next (created on first use)
     cudaStream_t dd_stream[2] = {nullptr, nullptr};
     cudaEvent_t dd_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    // ... and its work buffers (direction words, boundary scratch, offsets, redo list): grow-only,
+    // kept for the life of the context so that no launch waits for an allocation
+    void *dd_mem[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    size_t dd_cap[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     std::vector<uint8_t> h_dist;  // host copy of the symmetric table
     // dense-alphabet tables of the thread-per-pair DP kernel, cached per id set
     vsk_idset tiny_key;
@@ -116,6 +120,7 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
 #define VSK_DP_DIRJOB(l2) ((l2) > 128)
 // vsk_dp_dir_begin marks the point of ctx->stream the side streams start from (call it before the
 // other DP kernels are enqueued so that they overlap); vsk_dp_dir_launch joins back into ctx->stream.
+// *redo / *redo_count point into the context's buffers (valid until the next call).
 int vsk_dp_dir_begin(vsk_ctx *ctx);
 int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids, const vsk_dp_job *d_jobs,
                       int64_t n, int32_t max_l1, int4 *d_out, vsk_dp_job **redo, int **redo_count);
