@@ -632,9 +632,15 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         const char *e = getenv("VSK_DP_DIR");
         return !(e && e[0] == '0');
     }();
+    static const bool use_dir_q8 = [] {
+        const char *e = getenv("VSK_DP_DIRQ8");
+        return !(e && e[0] == '0');
+    }();
+    const bool dir_q8 = use_dir && use_dir_q8 && n_q8 > 0;  // the 8-lane jobs take the direction-bit path too
+    const bool dir_any = use_dir && (n_warp > 0 || dir_q8);
     int64_t grid_w = 0;
     int stride_w = 0;
-    if (n_warp > 0) {
+    if (n_warp > 0 || dir_any) {  // vsk_dp_kernel also takes the pairs the direction-bit path hands back
         if (!g_dp_attr_set) {
             VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                (int)DP_SMEM_BYTES));
@@ -645,7 +651,7 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
                                                                      DP_SMEM_BYTES));
         if (per_sm < 1) per_sm = 1;
         int64_t grid = (int64_t)ctx->sm_count * per_sm;  // persistent: one wave, work pulled from a queue
-        const int64_t need = (n_warp + DP_WARPS - 1) / DP_WARPS;
+        const int64_t need = dir_any ? grid : (n_warp + DP_WARPS - 1) / DP_WARPS;
         if (grid > need) grid = need;
         const int stride = ((max_l1 + 31) / 32) * 32;
         const size_t bytes = (size_t)grid * DP_WARPS * (stride + stride / 4) * sizeof(int4);  // boundary + row records
@@ -658,18 +664,20 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         }
         grid_w = grid;
         stride_w = stride;
-        if (use_dir) {  // the direction-bit path forks here and overlaps the three kernels below
+        if (dir_any) {  // the direction-bit path forks here and overlaps the kernels below
             int rc = vsk_dp_dir_begin(ctx);
             if (rc) return rc;
         }
-        VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
-        vsk_dp_kernel<<<(unsigned)grid, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
-            d_left_ids, d_top_ids, d_jobs, (int)n_warp, ctx->d_dist, ctx->d_gapnd,
-            (int4 *)ctx->d_dp_scratch, stride, ctx->d_queue, d_out, nullptr, use_dir ? 1 : 0);
-        ctx->launches++;
-        VSK_CUDA(ctx, cudaGetLastError());
+        if (n_warp > 0) {
+            VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
+            vsk_dp_kernel<<<(unsigned)grid, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(
+                d_left_ids, d_top_ids, d_jobs, (int)n_warp, ctx->d_dist, ctx->d_gapnd,
+                (int4 *)ctx->d_dp_scratch, stride, ctx->d_queue, d_out, nullptr, use_dir ? 1 : 0);
+            ctx->launches++;
+            VSK_CUDA(ctx, cudaGetLastError());
+        }
     }
-    if (n_q8 > 0) {
+    if (n_q8 > 0 && !dir_q8) {
         const size_t smem = 2048 + 1024 + (size_t)K * K;
         if (!g_q8_attr_set) {
             VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_q8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -704,10 +712,11 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         ctx->launches++;
         VSK_CUDA(ctx, cudaGetLastError());
     }
-    if (n_warp > 0 && use_dir) {
+    if (dir_any) {
         vsk_dp_job *d_redo = nullptr;
         int *d_redo_n = nullptr;
-        int rc = vsk_dp_dir_launch(ctx, d_left_ids, d_top_ids, d_jobs, n_warp, max_l1, d_out, &d_redo, &d_redo_n);
+        int rc = vsk_dp_dir_launch(ctx, d_left_ids, d_top_ids, d_jobs, n_warp, dir_q8 ? n_q8 : 0, K, max_l1, d_out,
+                                   &d_redo, &d_redo_n);
         if (rc) return rc;
         if (d_redo) {  // pairs whose corner the band does not reach
             VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));

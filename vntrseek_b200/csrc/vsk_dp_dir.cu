@@ -340,9 +340,9 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
 __global__ void __launch_bounds__(DD_WARPS * 32)
 vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
                   const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
-                  const int *__restrict__ bounds, int batch, int64_t batch_words, const uint8_t *__restrict__ dist,
-                  const uint16_t *__restrict__ gapnd, int *scratch, int scratch_stride, uint32_t *__restrict__ dirbuf,
-                  int *queue, int4 *out) {
+                  const int *__restrict__ bounds, int batch, int64_t batch_words, int job_end,
+                  const uint8_t *__restrict__ dist, const uint16_t *__restrict__ gapnd, int *scratch, int scratch_stride,
+                  uint32_t *__restrict__ dirbuf, int *queue, int4 *out) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -352,7 +352,7 @@ vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restr
     // per-warp scratch slice: scratch_stride boundary distances + scratch_stride row records
     int *my_bscr = scratch + (size_t)(blockIdx.x * DD_WARPS + warp) * 2 * scratch_stride;
     uint32_t *my_rowrec = reinterpret_cast<uint32_t *>(my_bscr + scratch_stride);
-    const int lo_job = bounds[batch], hi_job = bounds[batch + 1];
+    const int lo_job = bounds[batch], hi_job = min(bounds[batch + 1], job_end);
     for (;;) {
         int ji = 0;
         if (lane == 0) ji = lo_job + atomicAdd(queue + batch, 1);
@@ -380,6 +380,139 @@ vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restr
     }
 }
 
+// ---- the same sweep for pairs of at most 128 columns: 8 lanes per pair -------------------------
+// Four pairs per warp, each group of 8 lanes with its own job loop and sync mask (as
+// vsk_dp_q8_kernel); one strip of 8*CPL columns (CPL 4/8/16 by the number of columns); costs from
+// the dense K x K table of the data set in shared memory, so no per-pair set-up.  Direction words
+// as above with 8 lanes instead of strips*32: word (row, lane) at lane*l1p + row.
+#define DQ_WARPS 4
+#define DQ_G 8
+
+__host__ __device__ inline int dq_cpl(int l2) { return l2 <= 32 ? 4 : l2 <= 64 ? 8 : 16; }
+
+template <int CPL>
+__device__ __forceinline__ void dq_pair(const vsk_dp_job &job, const uint16_t *__restrict__ L,
+                                        const uint16_t *__restrict__ Tp, const uint16_t *s_gapnd,
+                                        const uint8_t *s_dense, const uint8_t *s_ktab, int K, uint32_t *ring,
+                                        unsigned gmask, int glane, uint32_t *__restrict__ dir, int4 *out) {
+    const int l1 = job.l1, l2 = job.l2, br = job.br;
+    const bool banded = br >= 0;
+    const int cbase = glane * CPL;
+    int Hd[CPL], tb[CPL], gt[CPL];
+    int sd = 0;
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+        const int c = cbase + j;
+        const int id = (c < l2) ? (int)Tp[c] : 0;
+        gt[j] = s_gapnd[id] & 255;
+        tb[j] = s_dense[id];
+        sd += gt[j];
+        Hd[j] = sd;
+    }
+    int xd = sd;
+#pragma unroll
+    for (int o = 1; o < DQ_G; o <<= 1) {
+        const int a = __shfl_up_sync(gmask, xd, o, DQ_G);
+        if (glane >= o) xd += a;
+    }
+    const int ed = xd - sd;
+#pragma unroll
+    for (int j = 0; j < CPL; ++j) {
+        Hd[j] += ed;
+        if (banded && cbase + j + 1 > br) Hd[j] = VSK_BIG;  // profile.h:1801-1802
+    }
+    int dgd = ed;
+    if (banded && cbase > br) dgd = VSK_BIG;
+    int id_next = L[min(max(-glane, 0), l1 - 1)];
+    const int l1p = (l1 + 7) & ~7;
+    uint32_t *dlane = dir + (size_t)glane * l1p;
+
+    auto step = [&](const int s, const bool check) {
+        const int r = s - glane;
+        int lfd = __shfl_up_sync(gmask, Hd[CPL - 1], 1, DQ_G);
+        const bool active = !check || ((r >= 0) && (r < l1));
+        const int id = id_next;
+        id_next = L[min(max(r + 1, 0), l1 - 1)];
+        const int gl = s_gapnd[id] & 255;
+        const uint8_t *trow = s_ktab + (int)s_dense[id] * K;
+        if (active) {
+            if (glane == 0) lfd = dgd + gl;  // column 0, profile.h:2084-2090
+            const uint32_t w = dd_row_cells<CPL, true>(Hd, tb, gt, dgd, lfd, trow, gl);
+            dgd = lfd;
+            ring[r & 15] = w;
+        }
+        if ((s & 7) == 7) {  // the lane's last complete group of 8 rows goes out as one sector
+            const int g0 = ((min(r, l1 - 1) + 1) & ~7) - 8;
+            if (g0 >= 0) {
+                const uint4 a = *reinterpret_cast<const uint4 *>(ring + (g0 & 15));
+                const uint4 b = *reinterpret_cast<const uint4 *>(ring + (g0 & 15) + 4);
+                uint4 *dst = reinterpret_cast<uint4 *>(dlane + g0);
+                __stcs(dst, a);
+                __stcs(dst + 1, b);
+            }
+        }
+    };
+    const int s_fill_end = min(DQ_G - 1, l1 + DQ_G - 1);
+    int s = 0;
+    for (; s < s_fill_end; ++s) step(s, true);
+    for (; s < l1; ++s) step(s, false);
+    for (; s < l1 + DQ_G - 1; ++s) step(s, true);
+    {  // the rows after the last complete group (and that group once more)
+        const int ga = (l1 - 1) & ~7;
+#pragma unroll
+        for (int g0 = ga - 8; g0 <= ga; g0 += 8) {
+            if (g0 < 0) continue;
+            const uint4 a = *reinterpret_cast<const uint4 *>(ring + (g0 & 15));
+            const uint4 b = *reinterpret_cast<const uint4 *>(ring + (g0 & 15) + 4);
+            uint4 *dst = reinterpret_cast<uint4 *>(dlane + g0);
+            __stcs(dst, a);
+            __stcs(dst + 1, b);
+        }
+    }
+    const int cl = l2 - 1;
+    if (glane == cl / CPL) {
+        const int jr = cl % CPL;
+#pragma unroll
+        for (int j = 0; j < CPL; ++j)
+            if (j == jr) out[job.out_idx] = make_int4(Hd[j], 0, 0, 0);
+    }
+}
+
+// jobs[q_begin..q_end) are the 8-lane jobs; a batch takes the part of its range that lies in there
+__global__ void __launch_bounds__(DQ_WARPS * 32)
+vsk_dp_q8dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
+                    const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
+                    const int *__restrict__ bounds, int batch, int64_t batch_words, int q_begin, int q_end,
+                    const uint8_t *__restrict__ dense, const uint8_t *__restrict__ ktab, int K,
+                    const uint16_t *__restrict__ gapnd, uint32_t *__restrict__ dirbuf, int *queue, int4 *out) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(smem);
+    uint32_t *s_ring = reinterpret_cast<uint32_t *>(smem + 2048);  // [thread][16]
+    uint8_t *s_dense = smem + 2048 + DQ_WARPS * 32 * 64;
+    uint8_t *s_ktab = s_dense + 1024;
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) { s_gapnd[i] = gapnd[i]; s_dense[i] = dense[i]; }
+    for (int i = threadIdx.x; i < K * K; i += blockDim.x) s_ktab[i] = ktab[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, glane = lane & (DQ_G - 1);
+    const unsigned gmask = 0xffu << (lane & ~(DQ_G - 1));
+    uint32_t *ring = s_ring + threadIdx.x * 16;
+    const int lo_job = max(bounds[batch], q_begin), hi_job = min(bounds[batch + 1], q_end);
+    for (;;) {
+        int ji = 0;
+        if (glane == 0) ji = lo_job + atomicAdd(queue, 1);
+        ji = __shfl_sync(gmask, ji, 0, DQ_G);
+        if (ji >= hi_job) break;
+        const vsk_dp_job job = jobs[ji];
+        const uint16_t *L = left_ids + job.left_off;
+        const uint16_t *Tp = top_ids + job.top_off;
+        uint32_t *dir = dirbuf + (dir_off[ji] - (int64_t)batch * batch_words);
+        if (job.l2 <= 32) dq_pair<4>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, ring, gmask, glane, dir, out);
+        else if (job.l2 <= 64) dq_pair<8>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, ring, gmask, glane, dir, out);
+        else dq_pair<16>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, ring, gmask, glane, dir, out);
+        __syncwarp(gmask);
+    }
+}
+
 // Trace: one thread per pair walks the stored directions from (l1,l2) to (0,0) and sums what the
 // reference's traceback sums (profile.h:2135-2210): dashnum*cost, dashnum, path length.
 //
@@ -399,14 +532,15 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
                     const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
                     const int *__restrict__ bounds, int batch, int64_t batch_words, const uint8_t *__restrict__ dist,
                     const uint16_t *__restrict__ gapnd, const uint32_t *__restrict__ dirbuf, int4 *out,
-                    vsk_dp_job *redo, int *redo_count) {
+                    vsk_dp_job *redo, int *redo_count, int q_begin) {
     __shared__ uint16_t s_gapnd[1024];
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_gapnd[i] = gapnd[i];
     __syncthreads();
     const int lo_job = bounds[batch], hi_job = bounds[batch + 1];
     for (int ji = lo_job + blockIdx.x * blockDim.x + threadIdx.x; ji < hi_job; ji += gridDim.x * blockDim.x) {
+        const int64_t off0 = dir_off[ji];
+        if (dir_off[ji + 1] == off0) continue;  // not a job of this path
         const vsk_dp_job job = jobs[ji];
-        if (!VSK_DP_DIRJOB(job.l2)) continue;
         const int d = out[job.out_idx].x;
         if (d >= VSK_BIG) {
             redo[atomicAdd(redo_count, 1)] = job;
@@ -414,10 +548,11 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
         }
         const uint16_t *L = left_ids + job.left_off;
         const uint16_t *Tp = top_ids + job.top_off;
-        const uint32_t *dir = dirbuf + (dir_off[ji] - (int64_t)batch * batch_words);
+        const uint32_t *dir = dirbuf + (off0 - (int64_t)batch * batch_words);
         const int l1p = (job.l1 + 7) & ~7;
         int cpl, ns;
-        dd_plan(job.l1, job.l2, cpl, ns);
+        if (ji >= q_begin) cpl = dq_cpl(job.l2);  // 8-lane job
+        else dd_plan(job.l1, job.l2, cpl, ns);
         int r = job.l1, c = job.l2;
         int p1 = 0, sumw = 0, len = 0;
         // position of column c-1 inside the strips: strip*32 + lane, cell
@@ -502,14 +637,20 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
     }
 }
 
-// direction words a job needs (0 = not a job for this path)
-__global__ void vsk_dd_words_kernel(const vsk_dp_job *__restrict__ jobs, int n, int64_t *__restrict__ words) {
+// direction words a job needs (0 = not a job for this path); jobs[q_begin..n) are the 8-lane jobs
+__global__ void vsk_dd_words_kernel(const vsk_dp_job *__restrict__ jobs, int n, int q_begin,
+                                    int64_t *__restrict__ words) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int l1 = jobs[i].l1, l2 = jobs[i].l2;
+    const int64_t l1p = (l1 + 7) & ~7;
+    if (i >= q_begin) {
+        words[i] = DQ_G * l1p;
+        return;
+    }
     int cpl, ns;
     dd_plan(l1, l2, cpl, ns);
-    words[i] = VSK_DP_DIRJOB(l2) ? (int64_t)ns * 32 * ((l1 + 7) & ~7) : 0;
+    words[i] = VSK_DP_DIRJOB(l2) ? (int64_t)ns * 32 * l1p : 0;
 }
 
 // bounds[b] = first job whose direction words start at or after b*batch_words (jobs of a batch are
@@ -563,9 +704,11 @@ static int dd_reserve(vsk_ctx *ctx, int k, size_t bytes, void **out) {
 // end.  *redo / *redo_count (device, owned by the context) receive the pairs that must go through
 // vsk_dp_kernel; both stay null when no job qualified.
 int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids, const vsk_dp_job *d_jobs,
-                      int64_t n, int32_t max_l1, int4 *d_out, vsk_dp_job **redo, int **redo_count) {
+                      int64_t n_warp, int64_t n_q8, int K, int32_t max_l1, int4 *d_out, vsk_dp_job **redo,
+                      int **redo_count) {
     *redo = nullptr;
     *redo_count = nullptr;
+    const int64_t n = n_warp + n_q8;  // the 8-lane jobs follow the warp-per-pair jobs
     if (n <= 0) return VSK_OK;
     cudaStream_t s0 = ctx->dd_stream[0], s1 = ctx->dd_stream[1];
     int rc;
@@ -578,12 +721,13 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     if ((rc = dd_reserve(ctx, 2, tmp_bytes + 16, &d_tmp))) return rc;
     VSK_CUDA(ctx, cudaStreamWaitEvent(s0, ctx->dd_ev[0], 0));
     VSK_CUDA(ctx, cudaMemsetAsync(d_words + n, 0, sizeof(int64_t), s0));
-    vsk_dd_words_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s0>>>(d_jobs, (int)n, d_words);
+    vsk_dd_words_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s0>>>(d_jobs, (int)n, (int)n_warp, d_words);
     ctx->launches++;
     VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
     ctx->launches += 2;
-    int64_t total = 0;
+    int64_t total = 0, off_q8 = 0;  // all words; words before the first 8-lane job
     VSK_CUDA(ctx, cudaMemcpyAsync(&total, d_off + n, sizeof(int64_t), cudaMemcpyDeviceToHost, s0));
+    VSK_CUDA(ctx, cudaMemcpyAsync(&off_q8, d_off + n_warp, sizeof(int64_t), cudaMemcpyDeviceToHost, s0));
     VSK_CUDA(ctx, cudaStreamSynchronize(s0));
     if (total == 0) {
         VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[2], s0));
@@ -614,6 +758,20 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
                                                                  dd_smem));
     if (per_sm < 1) per_sm = 1;
     const int grid = ctx->sm_count * per_sm;
+    // the 8-lane kernel
+    const size_t dq_smem = 2048 + DQ_WARPS * 32 * 64 + 1024 + (size_t)K * K;
+    int grid8 = 0;
+    if (n_q8 > 0) {
+        static int attr8 = 0;
+        if (!attr8) {
+            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_q8dir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               2048 + DQ_WARPS * 32 * 64 + 1024 + 200 * 200));
+            attr8 = 1;
+        }
+        int per_sm8 = 0;
+        VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm8, vsk_dp_q8dir_kernel, DQ_WARPS * 32, dq_smem));
+        grid8 = ctx->sm_count * (per_sm8 < 1 ? 1 : per_sm8);
+    }
     const int stride = ((max_l1 + 31) / 32) * 32 + 128;  // slack: the steady phase fetches up to 96 rows past the last
     const size_t scr_ints = (size_t)grid * DD_WARPS * 2 * stride;
 
@@ -621,27 +779,37 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     int *d_small = nullptr, *d_scr = nullptr;
     if ((rc = dd_reserve(ctx, 3, (size_t)half_words * nhalf * 4, (void **)&d_dir))) return rc;
     if ((rc = dd_reserve(ctx, 4, scr_ints * 2 * sizeof(int), (void **)&d_scr))) return rc;
-    if ((rc = dd_reserve(ctx, 5, (size_t)(2 * (nb + 1) + 1) * sizeof(int), (void **)&d_small))) return rc;
+    if ((rc = dd_reserve(ctx, 5, (size_t)(3 * (nb + 1) + 1) * sizeof(int), (void **)&d_small))) return rc;
     if ((rc = dd_reserve(ctx, 6, (size_t)n * sizeof(vsk_dp_job), (void **)redo))) return rc;
-    int *d_bounds = d_small, *d_queue = d_small + (nb + 1);
-    *redo_count = d_small + 2 * (nb + 1);
-    VSK_CUDA(ctx, cudaMemsetAsync(d_queue, 0, (size_t)(nb + 2) * sizeof(int), s0));  // queue heads + redo count
+    int *d_bounds = d_small, *d_queue = d_small + (nb + 1), *d_queue8 = d_small + 2 * (nb + 1);
+    *redo_count = d_small + 3 * (nb + 1);
+    VSK_CUDA(ctx, cudaMemsetAsync(d_queue, 0, (size_t)(2 * (nb + 1) + 1) * sizeof(int), s0));  // queue heads + redo count
     vsk_dd_bounds_kernel<<<(nb + 1 + 127) / 128, 128, 0, s0>>>(d_off, (int)n, batch_words, nb, d_bounds);
     ctx->launches++;
     VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[1], s0));
     VSK_CUDA(ctx, cudaStreamWaitEvent(s1, ctx->dd_ev[1], 0));  // s1 starts after the batch bounds exist
 
+    const int h_q8_first = (int)(off_q8 / batch_words);  // first batch with 8-lane jobs
     for (int b = 0; b < nb; ++b) {
         cudaStream_t st = (b & 1) ? s1 : s0;
         uint32_t *dir = d_dir + (size_t)(b & 1) * half_words;
         int *scr = d_scr + (size_t)(b & 1) * scr_ints;
-        vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, dd_smem, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
-                                                                batch_words, ctx->d_dist, ctx->d_gapnd, scr, stride, dir,
-                                                                d_queue, d_out);
+        if (n_warp > 0 && b <= h_q8_first) {
+            vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, dd_smem, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
+                                                                    batch_words, (int)n_warp, ctx->d_dist, ctx->d_gapnd,
+                                                                    scr, stride, dir, d_queue, d_out);
+            ctx->launches++;
+        }
+        if (n_q8 > 0 && b >= h_q8_first) {
+            vsk_dp_q8dir_kernel<<<grid8, DQ_WARPS * 32, dq_smem, st>>>(
+                d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b, batch_words, (int)n_warp, (int)n, ctx->d_tiny_dense,
+                ctx->d_tiny_ktab, K, ctx->d_gapnd, dir, d_queue8 + b, d_out);
+            ctx->launches++;
+        }
         vsk_dp_trace_kernel<<<ctx->sm_count * 8, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
                                                                        batch_words, ctx->d_dist, ctx->d_gapnd, dir,
-                                                                       d_out, *redo, *redo_count);
-        ctx->launches += 2;
+                                                                       d_out, *redo, *redo_count, (int)n_warp);
+        ctx->launches++;
     }
     VSK_CUDA(ctx, cudaGetLastError());
     // join: ctx->stream continues after both side streams

@@ -122,8 +122,11 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
 // other DP kernels are enqueued so that they overlap); vsk_dp_dir_launch joins back into ctx->stream.
 // *redo / *redo_count point into the context's buffers (valid until the next call).
 int vsk_dp_dir_begin(vsk_ctx *ctx);
+// d_jobs[0..n_warp) are the warp-per-pair jobs, d_jobs[n_warp..n_warp+n_q8) the 8-lane jobs (dense
+// K x K table of the context).
 int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids, const vsk_dp_job *d_jobs,
-                      int64_t n, int32_t max_l1, int4 *d_out, vsk_dp_job **redo, int **redo_count);
+                      int64_t n_warp, int64_t n_q8, int K, int32_t max_l1, int4 *d_out, vsk_dp_job **redo,
+                      int **redo_count);
 // which composition ids occur in d_ids[0..n)
 int vsk_id_presence(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out);
 
