@@ -337,7 +337,10 @@ __global__ void __launch_bounds__(256)
 vsk_seed_kernel(DevTR reads, DevIndex idx, DevLuts luts, int32_t p_begin, int32_t p_end,
                 int64_t *__restrict__ cnt_emit, unsigned long long *__restrict__ raw_total,
                 const int64_t *__restrict__ off_emit, int64_t base, int key_shift,
-                uint64_t *__restrict__ keys) {
+                uint64_t *__restrict__ keys, uint64_t *__restrict__ wcache) {
+    // wcache[consensus position] = what the count pass found for the window that ends there
+    // (first entry << 26 | entries << 1 | extra; 0 = nothing to emit), so that the fill pass does not
+    // search again
     const int lane = threadIdx.x & 31;
     const int32_t p = p_begin + (int32_t)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5);
     if (p >= p_end) return;
@@ -359,23 +362,35 @@ vsk_seed_kernel(DevTR reads, DevIndex idx, DevLuts luts, int32_t p_begin, int32_
             w.s = w.e2 = 0;
             w.extra = 0;
             bool found = false;
-            uint64_t code = ~0ull;  // no window position (cannot equal a real code: those use < 60 bits)
-            if (i < len) {
-                uint32_t c1 = 0, c2 = 0;
-                for (int k = 0; k < nones; ++k) {
-                    const uint32_t b = (uint32_t)base_code(seq[i + c_seed_off[t][k]]);
-                    if (k <= 14) c1 = c1 * 4 + b;
-                    else c2 = c2 * 4 + b;
+            int mult = 1;
+            if (FILL) {
+                const uint64_t pk = (i < len) ? wcache[reads.cons_off[p] + i] : 0ull;
+                found = pk != 0ull;
+                w.s = (int64_t)(pk >> 26);
+                w.e2 = w.s + (int64_t)((pk >> 1) & 0x1ffffffull);
+                w.extra = (int)(pk & 1ull);
+            } else {
+                uint64_t code = ~0ull;  // no window position (cannot equal a real code: those use < 60 bits)
+                if (i < len) {
+                    uint32_t c1 = 0, c2 = 0;
+                    for (int k = 0; k < nones; ++k) {
+                        const uint32_t b = (uint32_t)base_code(seq[i + c_seed_off[t][k]]);
+                        if (k <= 14) c1 = c1 * 4 + b;
+                        else c2 = c2 * 4 + b;
+                    }
+                    code = ((uint64_t)c1 << 32) | c2;
                 }
-                code = ((uint64_t)c1 << 32) | c2;
+                // periodic (low-complexity) consensus strings repeat the same seed code every few positions:
+                // only the first lane of each group of equal codes looks the bucket up and emits keys; the
+                // CandidatesConsidered counter still counts the window once per position (`mult` lanes)
+                const unsigned same = __match_any_sync(0xffffffffu, code);
+                const bool leader = (i < len) && (lane == __ffs(same) - 1);
+                mult = __popc(same);
+                if (leader) found = seed_lookup(idx, t, code, lo, hi, w);
+                if (i < len)
+                    wcache[reads.cons_off[p] + i] =
+                        found ? (((uint64_t)w.s << 26) | ((uint64_t)(w.e2 - w.s) << 1) | (uint64_t)w.extra) : 0ull;
             }
-            // periodic (low-complexity) consensus strings repeat the same seed code every few positions:
-            // only the first lane of each group of equal codes looks the bucket up and emits keys; the
-            // CandidatesConsidered counter still counts the window once per position (`mult` lanes)
-            const unsigned same = __match_any_sync(0xffffffffu, code);
-            const bool leader = (i < len) && (lane == __ffs(same) - 1);
-            const int mult = __popc(same);
-            if (leader) found = seed_lookup(idx, t, code, lo, hi, w);
             const int64_t nd = found ? (w.e2 - w.s + w.extra) : 0;
             if (!FILL) {
                 emit += nd;
@@ -823,7 +838,7 @@ static void keep_pool(vsk_ctx *ctx) {
 
 static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const vsk_proclu_params *prm,
                      int32_t p_begin, int32_t p_end, const int64_t *d_off_emit, int64_t base, int64_t nkeys,
-                     vsk_proclu_result *out) {
+                     uint64_t *d_wcache, vsk_proclu_result *out) {
     if (nkeys == 0) return VSK_OK;
     cudaStream_t st = ctx->stream;
     Scratch S(ctx);
@@ -845,7 +860,8 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     int end_bit = key_shift + 1;
     while (end_bit < 64 && ((uint64_t)(nprof - 1) >> (end_bit - key_shift))) ++end_bit;
     vsk_seed_kernel<true><<<blocks(nprof * 32, 256), 256, 0, st>>>(reads, R->idx, R->luts, p_begin, p_end,
-                                                                   nullptr, nullptr, d_off_emit, base, key_shift, keys);
+                                                                   nullptr, nullptr, d_off_emit, base, key_shift, keys,
+                                                                   d_wcache);
     ctx->launches++;
     vsk_stage_mark(ctx, "seed_fill");
     // candsort + dedup
@@ -1045,6 +1061,8 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         }
     }
     Q->checked = true;
+    if (2 * (int64_t)R->tr->d.n >= (1 << 25))  // a seed bucket holds at most one entry per reference profile
+        return vsk_fail(ctx, VSK_ERR_ARG, "more than 2^24 reference TRs: the seed-window records do not hold them");
     vsk_proclu_result *res = new vsk_proclu_result();
     res->ctx = ctx;
     memset(&res->stats, 0, sizeof res->stats);
@@ -1057,8 +1075,9 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         int64_t *cnt, *off;
         unsigned long long *raw;
         cudaError_t e;
+        uint64_t *wcache;  // one word per consensus character of the reads: the seed windows the count pass found
         if ((e = S.get(&cnt, (size_t)nprof + 1)) != cudaSuccess || (e = S.get(&off, (size_t)nprof + 1)) != cudaSuccess ||
-            (e = S.get(&raw, 1)) != cudaSuccess) {
+            (e = S.get(&raw, 1)) != cudaSuccess || (e = S.get(&wcache, hq->cons.size() + 1)) != cudaSuccess) {
             delete res;
             return vsk_fail(ctx, VSK_ERR_CUDA, "alloc: %s", cudaGetErrorString(e));
         }
@@ -1066,7 +1085,7 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         cudaMemsetAsync(raw, 0, sizeof(unsigned long long), st);
         cudaMemsetAsync(cnt + nprof, 0, sizeof(int64_t), st);
         vsk_seed_kernel<false><<<blocks((int64_t)nprof * 32, 256), 256, 0, st>>>(Q->d, R->idx, R->luts, 0, nprof, cnt,
-                                                                                raw, nullptr, 0, 0, nullptr);
+                                                                                raw, nullptr, 0, 0, nullptr, wcache);
         ctx->launches++;
         size_t tb = 0;
         cub::DeviceScan::ExclusiveSum(nullptr, tb, cnt, off, nprof + 1, st);
@@ -1100,7 +1119,7 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         while (pb < nprof && rc == VSK_OK) {
             int32_t pe = pb + 2;
             while (pe < nprof && hoff[(size_t)pe + 2] - hoff[(size_t)pb] <= budget) pe += 2;
-            rc = run_chunk(ctx, R, Q, prm, pb, pe, off, hoff[(size_t)pb], hoff[(size_t)pe] - hoff[(size_t)pb], res);
+            rc = run_chunk(ctx, R, Q, prm, pb, pe, off, hoff[(size_t)pb], hoff[(size_t)pe] - hoff[(size_t)pb], wcache, res);
             res->stats.chunks++;
             pb = pe;
         }
