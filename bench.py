@@ -31,6 +31,7 @@ sys.path.insert(0, ROOT)
 
 import numpy as np  # noqa: E402
 
+DIR_TRAFFIC = None  # bytes; filled in from the ncu capture under profiles/
 METRIC = "proclu_read_TRs_mapped_per_sec"
 UNIT = "read-TRs/s"
 
@@ -369,10 +370,13 @@ def ours(args, rank, world, local_rank):
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                          "frac": achieved_gbs / peaks.get("hbm_gbs", 1.0),
-                         "traffic": 1.96e9 if args.nreads == 1000000 and args.nref == 250000 else None,
-                         "traffic_note": "dram__bytes_read+write of one vsk_dp_kernel launch (first chunk), ncu --set full, "
-                                         "profiles/r01_summary.md; boundary/row-record scratch dominates it",
-                         "kernel": "vsk_dp_kernel (+ vsk_dp_q8_kernel, vsk_dp_tiny_kernel: the three size classes of the profile DP)", "kernel_ms_per_step": dp_ms / K,
+                         "traffic": DIR_TRAFFIC if args.nreads == 1000000 and args.nref == 250000 else None,
+                         "traffic_note": "dram__bytes_read+write of one vsk_dp_dir_kernel launch (first 4 GiB batch of the "
+                                         "first chunk), ncu --set full, profiles/r01_summary.md; the direction words "
+                                         "(0.25 B per cell) are all of it",
+                         "kernel": "vsk_dp_dir_kernel (forward sweep of the profile DP; the DP stage timed here also holds "
+                                   "vsk_dp_q8dir_kernel, vsk_dp_tiny_kernel and vsk_dp_trace_kernel)",
+                         "kernel_ms_per_step": dp_ms / K,
                          "kernel_share_of_step": (dp_ms / K) / step_ms, "peak_source": peak_src,
                          "note": "integer DP: issue/ALU bound, HBM fraction is evidence of non-boundness; see int_alu"},
             "int_alu": {"achieved": int_ops, "peak": int_peak, "unit": "Gop/s", "frac": int_ops / int_peak if int_peak else None,

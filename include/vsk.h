@@ -99,7 +99,7 @@ void vsk_dp_batch_free(vsk_ctx *ctx, vsk_dp_batch *b);
  * caller's own pool allocator, the call sits in a latency-critical section where the
  * device-wide synchronisation of cudaMalloc/cudaFree is unacceptable, or the memory
  * budget was fixed at start-up.)
- * Same kernel and results as vsk_pair_dp.  The caller passes the inputs and the output
+ * Same results as vsk_pair_dp (it runs the one-kernel DP, which holds no direction words).  The caller passes the inputs and the output
  * as DEVICE pointers (composition ids of both profile sets, n results) and the pair
  * descriptors as a HOST array; the boundary-column scratch, the device copy of the
  * descriptors and the work counter live in one fixed device array inside libvsk.so

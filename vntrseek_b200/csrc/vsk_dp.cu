@@ -740,8 +740,9 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
 // alignment: a service that has handed the whole GPU to its own pool allocator, a
 // latency-critical section between two of the caller's launches where the implicit
 // device synchronisation of cudaMalloc/cudaFree is not acceptable, or a process whose
-// memory budget was fixed at start-up.  vsk_pair_dp_static runs the same kernel as
-// vsk_pair_dp, but everything that call would allocate (the boundary-column scratch of
+// memory budget was fixed at start-up.  vsk_pair_dp_static gives the results of
+// vsk_pair_dp through vsk_dp_kernel alone (the one-kernel variant, which has no buffer of
+// direction words to hold), and everything it needs (the boundary-column scratch of
 // the column strips, the device copy of the pair descriptors, the work counter) lives
 // in one file-scope device array of fixed size that every GPU loading libvsk.so holds
 // until the process exits.
