@@ -371,7 +371,7 @@ def ours(args, rank, world, local_rank):
             "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                          "frac": achieved_gbs / peaks.get("hbm_gbs", 1.0),
                          "traffic": DIR_TRAFFIC if args.nreads == 1000000 and args.nref == 250000 else None,
-                         "traffic_note": "dram__bytes_read+write of one vsk_dp_dir_kernel launch (first 4 GiB batch of the "
+                         "traffic_note": "dram__bytes_read+write of one vsk_dp_dir_kernel launch (first 12 GiB batch of the "
                                          "first chunk), ncu --set full, profiles/r01_summary.md; the direction words "
                                          "(0.25 B per cell) are all of it",
                          "kernel": "vsk_dp_dir_kernel (forward sweep of the profile DP; the DP stage timed here also holds "

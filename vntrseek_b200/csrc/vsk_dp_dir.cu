@@ -337,7 +337,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
 }
 
 // forward sweep: jobs[0..n) with their direction-word offsets dir_off[] into dirbuf
-__global__ void __launch_bounds__(DD_WARPS * 32)
+__global__ void __maxnreg__(120)
 vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
                   const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
                   const int *__restrict__ bounds, int batch, int64_t batch_words, int job_end,
@@ -524,7 +524,7 @@ vsk_dp_q8dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
 // picks the same candidate.  The trace checks every cell of the path against the band; a pair whose
 // path leaves it -- or whose corner is unreachable (distance >= BIG) -- is handed back on `redo`
 // and goes through vsk_dp_kernel, which masks cell by cell.
-#define DT_THREADS 128
+#define DT_THREADS 64
 #define DT_AHEAD 24
 
 __global__ void __launch_bounds__(DT_THREADS)
@@ -734,9 +734,9 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
         VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[2], 0));
         return VSK_OK;
     }
-    // batch size: VSK_DIR_BATCH_MB of direction words per stream (default 4 GiB), at most a sixth of the
+    // batch size: VSK_DIR_BATCH_MB of direction words per stream (default 12 GiB), at most a sixth of the
     // memory that is free or already ours
-    int64_t batch_mb = 4096;
+    int64_t batch_mb = 12288;
     if (const char *e = getenv("VSK_DIR_BATCH_MB")) batch_mb = std::max<int64_t>(16, atoll(e));
     size_t free_b = 0, total_b = 0;
     VSK_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
@@ -806,7 +806,7 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
                 ctx->d_tiny_ktab, K, ctx->d_gapnd, dir, d_queue8 + b, d_out);
             ctx->launches++;
         }
-        vsk_dp_trace_kernel<<<ctx->sm_count * 8, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
+        vsk_dp_trace_kernel<<<ctx->sm_count * 16, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
                                                                        batch_words, ctx->d_dist, ctx->d_gapnd, dir,
                                                                        d_out, *redo, *redo_count, (int)n_warp);
         ctx->launches++;
