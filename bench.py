@@ -31,7 +31,7 @@ sys.path.insert(0, ROOT)
 
 import numpy as np  # noqa: E402
 
-DIR_TRAFFIC = None  # bytes; filled in from the ncu capture under profiles/
+DIR_TRAFFIC = 11.01e9  # bytes: dram read+write of the first vsk_dp_dir_kernel launch, profiles/r01_summary.md (r01g)
 METRIC = "proclu_read_TRs_mapped_per_sec"
 UNIT = "read-TRs/s"
 
@@ -373,7 +373,8 @@ def ours(args, rank, world, local_rank):
                          "traffic": DIR_TRAFFIC if args.nreads == 1000000 and args.nref == 250000 else None,
                          "traffic_note": "dram__bytes_read+write of one vsk_dp_dir_kernel launch (first 12 GiB batch of the "
                                          "first chunk), ncu --set full, profiles/r01_summary.md; the direction words "
-                                         "(0.25 B per cell) are all of it",
+                                         "(0.25 B per cell) are all of it; a step has about 9 such launches, while "
+                                         "`achieved` is over the whole DP stage of a chunk",
                          "kernel": "vsk_dp_dir_kernel (forward sweep of the profile DP; the DP stage timed here also holds "
                                    "vsk_dp_q8dir_kernel, vsk_dp_tiny_kernel and vsk_dp_trace_kernel)",
                          "kernel_ms_per_step": dp_ms / K,
