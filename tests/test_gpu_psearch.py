@@ -79,6 +79,28 @@ def test_psearch_golden_small(tmp_path, dst_file):
     assert canonical_clu(os.path.join(w, "reads.leb36.clu")) == canonical_clu(os.path.join(w, "expected.clu"))
 
 
+@pytest.mark.parametrize("switch", ["VSK_DEDUP_BITMAP", "VSK_DP_DIR", "VSK_DP_DIRQ8"])
+def test_alternative_paths_give_the_same_files(tmp_path, dst_file, switch):
+    """the run-time switches select the older code paths (radix sort + unique instead of the
+    per-profile bitmap; one-kernel DP instead of sweep + trace): same counters, same .clu"""
+    from conftest import GOLDEN
+    g = os.path.join(GOLDEN, "psearch_small")
+    outs = []
+    for val in (None, "0"):
+        w = str(tmp_path / ("w" + str(val)))
+        shutil.copytree(g, w)
+        os.remove(os.path.join(w, "reads.leb36.clu"))
+        env = dict(os.environ)
+        if val is not None:
+            env[switch] = val
+        rc, _, log = run(os.path.join(OUR_BIN, "psearch.exe"), ["reference.leb36", "reads.leb36", dst_file, 88, 0, 50], w,
+                         env=env)
+        assert rc == 0, log[-500:]
+        outs.append((parse_counters(log), open(os.path.join(w, "reads.leb36.clu")).read()))
+    assert outs[0] == outs[1]
+    assert outs[0][0] == parse_counters(open(os.path.join(g, "ref.log")).read())
+
+
 def test_edges_mode_byte_exact(tmp_path, dst_file):
     if not _have_ref():
         pytest.skip("oracle/_ref/psearch.exe not built")

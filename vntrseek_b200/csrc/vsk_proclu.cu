@@ -814,6 +814,113 @@ struct vsk_proclu_result {
     }
 };
 
+// ---- candsort + dedup without a sort ----------------------------------------------------
+// The keys of one read profile are contiguous (the seed kernel writes them at the profile's
+// offset), so "sort by (read, ref) and drop duplicates" is, per read profile, "which reference
+// profiles occur": a block sets one bit per key in a shared-memory bitmap over the reference
+// profiles and reads the set bits back in ascending order (clearing them for the next profile).
+// The unique keys go back to the start of the profile's own segment, widened to
+// (read profile << 32 | reference profile); vsk_compact_kernel then closes the gaps.
+#define DEDUP_THREADS 256
+
+// bitmap of `nwords` 32-bit words + a summary with one bit per bitmap word (only the words that
+// were touched are visited when the bits are read back); thread t owns SW consecutive summary words
+__global__ void __launch_bounds__(DEDUP_THREADS)
+vsk_dedup_kernel(uint64_t *__restrict__ keys, const int64_t *__restrict__ off_emit, int64_t base, int32_t p_begin,
+                 int32_t nprof, int nwords, uint64_t refmask, int *__restrict__ counter, int64_t *__restrict__ ucount) {
+    extern __shared__ uint32_t s_bm[];
+    __shared__ int s_q;
+    __shared__ int s_wsum[DEDUP_THREADS / 32];
+    const int nsum = (nwords + 31) >> 5;
+    const int SW = (nsum + DEDUP_THREADS - 1) / DEDUP_THREADS;
+    uint32_t *bm = s_bm, *sum = s_bm + nwords;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < nwords + nsum; i += DEDUP_THREADS) s_bm[i] = 0;
+    const int sw0 = min(tid * SW, nsum), sw1 = min(sw0 + SW, nsum);
+    for (;;) {
+        __syncthreads();  // everybody is done with s_q (and the bitmap is clean)
+        if (tid == 0) {   // next profile that has keys
+            int q;
+            for (;;) {
+                q = atomicAdd(counter, 1);
+                if (q >= nprof || off_emit[p_begin + q + 1] != off_emit[p_begin + q]) break;
+                ucount[q] = 0;
+            }
+            s_q = q;
+        }
+        __syncthreads();
+        const int q = s_q;
+        if (q >= nprof) break;
+        const int64_t s0 = off_emit[p_begin + q] - base;
+        const int64_t n = off_emit[p_begin + q + 1] - base - s0;
+        for (int64_t i = tid; i < n; i += DEDUP_THREADS) {
+            const uint32_t ref = (uint32_t)(keys[s0 + i] & refmask);
+            const uint32_t w = ref >> 5;
+            atomicOr(&bm[w], 1u << (ref & 31));
+            atomicOr(&sum[w >> 5], 1u << (w & 31));
+        }
+        __syncthreads();
+        int cnt = 0;
+        for (int sw = sw0; sw < sw1; ++sw) {
+            uint32_t m = sum[sw];
+            while (m) {
+                cnt += __popc(bm[sw * 32 + __ffs(m) - 1]);
+                m &= m - 1;
+            }
+        }
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        int woff = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < DEDUP_THREADS / 32; ++w) {
+            const int v = s_wsum[w];
+            if (w < warp) woff += v;
+            total += v;
+        }
+        if (cnt) {
+            const uint64_t hi = (uint64_t)(uint32_t)(p_begin + q) << 32;
+            int64_t dst = s0 + woff + incl - cnt;
+            for (int sw = sw0; sw < sw1; ++sw) {
+                uint32_t m = sum[sw];
+                if (!m) continue;
+                sum[sw] = 0;
+                while (m) {
+                    const int w = sw * 32 + __ffs(m) - 1;
+                    m &= m - 1;
+                    uint32_t b = bm[w];
+                    bm[w] = 0;
+                    while (b) {
+                        keys[dst++] = hi | (uint64_t)((uint32_t)w * 32u + (uint32_t)(__ffs(b) - 1));
+                        b &= b - 1;
+                    }
+                }
+            }
+        }
+        if (tid == 0) ucount[q] = total;
+    }
+}
+
+// warp per read profile: the unique keys of the profile move to their place in the dense pair list
+__global__ void __launch_bounds__(256)
+vsk_compact_kernel(const uint64_t *__restrict__ keys, const int64_t *__restrict__ off_emit, int64_t base,
+                   int32_t p_begin, int32_t nprof, const int64_t *__restrict__ ucount,
+                   const int64_t *__restrict__ uoff, uint64_t *__restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (q >= nprof) return;
+    const int64_t n = ucount[q];
+    if (n == 0) return;
+    const uint64_t *src = keys + (off_emit[p_begin + q] - base);
+    uint64_t *dst = out + uoff[q];
+    for (int64_t i = lane; i < n; i += 32) dst[i] = src[i];
+}
+
 struct WidenKey {  // chunk-relative sort key -> (read profile << 32) | reference profile
     int shift;
     uint32_t p_begin;
@@ -864,21 +971,62 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
                                                                    d_wcache);
     ctx->launches++;
     vsk_stage_mark(ctx, "seed_fill");
-    // candsort + dedup
-    auto wide = thrust::make_transform_output_iterator(
-        keys, WidenKey{key_shift, (uint32_t)p_begin, ((uint64_t)1 << key_shift) - 1});
-    size_t tb = 0, tb2 = 0;
-    cub::DeviceRadixSort::SortKeys(nullptr, tb, keys, keys2, nkeys, 0, end_bit, st);
-    cub::DeviceSelect::Unique(nullptr, tb2, keys2, wide, d_n, nkeys, st);
-    tb = std::max(tb, tb2);
-    void *tmp;
-    VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb));
-    VSK_CUDA(ctx, cub::DeviceRadixSort::SortKeys(tmp, tb, keys, keys2, nkeys, 0, end_bit, st));
-    VSK_CUDA(ctx, cub::DeviceSelect::Unique(tmp, tb, keys2, wide, d_n, nkeys, st));
-    pairs = keys;
-    vsk_stage_mark(ctx, "sort_unique");
+    // candsort + dedup: per-profile bitmap when the reference profiles fit one in shared memory,
+    // else radix sort + unique
+    static const bool use_bitmap = [] {
+        const char *e = getenv("VSK_DEDUP_BITMAP");
+        return !(e && e[0] == '0');
+    }();
+    const int64_t bm_words = (2 * (int64_t)refs.n + 31) / 32;
+    size_t tb = 0;
+    void *tmp = nullptr;
     int64_t npairs = 0;
-    VSK_CUDA(ctx, cudaMemcpyAsync(&npairs, d_n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    if (use_bitmap && bm_words <= 48000 && nprof < 0x7fffffff) {
+        const size_t smem = (size_t)(bm_words + (bm_words + 31) / 32) * sizeof(uint32_t);
+        static int attr_set = 0;
+        if (!attr_set) {
+            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dedup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (48000 + 1500) * (int)sizeof(uint32_t)));
+            attr_set = 1;
+        }
+        int per_sm = 0;
+        VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dedup_kernel, DEDUP_THREADS, smem));
+        if (per_sm < 1) per_sm = 1;
+        int64_t *ucount, *uoff;
+        int *counter;
+        VSK_CUDA(ctx, S.get(&ucount, (size_t)nprof + 1));
+        VSK_CUDA(ctx, S.get(&uoff, (size_t)nprof + 1));
+        VSK_CUDA(ctx, S.get(&counter, 4));
+        VSK_CUDA(ctx, cudaMemsetAsync(counter, 0, sizeof(int), st));
+        VSK_CUDA(ctx, cudaMemsetAsync(ucount + nprof, 0, sizeof(int64_t), st));
+        vsk_dedup_kernel<<<(unsigned)(ctx->sm_count * per_sm), DEDUP_THREADS, smem, st>>>(
+            keys, d_off_emit, base, p_begin, (int32_t)nprof, (int)bm_words, ((uint64_t)1 << key_shift) - 1, counter, ucount);
+        VSK_CUDA(ctx, cudaGetLastError());
+        cub::DeviceScan::ExclusiveSum(nullptr, tb, ucount, uoff, (int)nprof + 1, st);
+        VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb));
+        VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, tb, ucount, uoff, (int)nprof + 1, st));
+        vsk_compact_kernel<<<blocks(nprof * 32, 256), 256, 0, st>>>(keys, d_off_emit, base, p_begin, (int32_t)nprof,
+                                                                   ucount, uoff, keys2);
+        ctx->launches += 2;
+        pairs = keys2;
+        pairs2 = keys;
+        vsk_stage_mark(ctx, "sort_unique");
+        VSK_CUDA(ctx, cudaMemcpyAsync(&npairs, uoff + nprof, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    } else {
+        auto wide = thrust::make_transform_output_iterator(
+            keys, WidenKey{key_shift, (uint32_t)p_begin, ((uint64_t)1 << key_shift) - 1});
+        size_t tb2 = 0;
+        cub::DeviceRadixSort::SortKeys(nullptr, tb, keys, keys2, nkeys, 0, end_bit, st);
+        cub::DeviceSelect::Unique(nullptr, tb2, keys2, wide, d_n, nkeys, st);
+        tb = std::max(tb, tb2);
+        VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb));
+        VSK_CUDA(ctx, cub::DeviceRadixSort::SortKeys(tmp, tb, keys, keys2, nkeys, 0, end_bit, st));
+        VSK_CUDA(ctx, cub::DeviceSelect::Unique(tmp, tb, keys2, wide, d_n, nkeys, st));
+        pairs = keys;
+        pairs2 = keys2;
+        vsk_stage_mark(ctx, "sort_unique");
+        VSK_CUDA(ctx, cudaMemcpyAsync(&npairs, d_n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    }
     VSK_CUDA(ctx, cudaStreamSynchronize(st));
     out->stats.lcs_alignments += (uint64_t)npairs;
     if (npairs == 0) return VSK_OK;
@@ -900,9 +1048,7 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
                                                                       long_ctr + 4, flags);
     vsk_lcs_sys_kernel<2><<<(unsigned)ctx->sm_count * 8, 128, 0, st>>>(refs, reads, R->luts, pairs, long_list, 1,
                                                                       long_ctr, long_ctr + 3, flags);
-    ctx->launches += 2;
     ctx->launches += 4;
-    pairs2 = keys2;
     size_t tb3 = 0;
     cub::DeviceSelect::Flagged(nullptr, tb3, pairs, flags, pairs2, d_n, npairs, st);
     if (tb3 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb3)); tb = tb3; }
