@@ -46,10 +46,16 @@ struct DevIndex {
     const uint64_t *codes[15];
     const int64_t *boff[15];
     int32_t ncodes[15];
+    // lut[t][code >> lut_shift[t]] = first code with that prefix (VSK_LUT_BITS bits, one more element
+    // at the end): the search for a code starts in its prefix's range instead of the whole array
+    const int32_t *lut[15];
+    int32_t lut_shift[15];
     const int16_t *e_pmin;
     const int32_t *e_prof, *e_first;
     const int64_t *e_gcum;  // exclusive prefix of the multiplicities over all entries (+1 element)
 };
+
+#define VSK_LUT_BITS 16
 
 struct DevLuts {
     const int16_t *trange_of, *err_of;  // [5001]
@@ -236,6 +242,22 @@ extern "C" int vsk_refs_create(vsk_ctx *ctx, const vsk_trset *refs, vsk_refs **o
         R->idx.codes[t] = dc;
         R->idx.boff[t] = db;
         R->idx.ncodes[t] = (int32_t)hi.codes[t].size();
+        {  // prefix table over the sorted codes
+            const std::vector<uint64_t> &cv = hi.codes[t];
+            int shift = 0;
+            if (!cv.empty())
+                while ((cv.back() >> shift) >> VSK_LUT_BITS) ++shift;
+            std::vector<int32_t> lut(((size_t)1 << VSK_LUT_BITS) + 1, (int32_t)cv.size());
+            size_t k = 0;
+            for (size_t pfx = 0; pfx < ((size_t)1 << VSK_LUT_BITS); ++pfx) {
+                while (k < cv.size() && (cv[k] >> shift) < pfx) ++k;
+                lut[pfx] = (int32_t)k;
+            }
+            int32_t *dl;
+            FAIL(upload_vec(ctx, R->allocs, lut, &dl));
+            R->idx.lut[t] = dl;
+            R->idx.lut_shift[t] = shift;
+        }
     }
     std::vector<int64_t> gcum(hi.e_mult.size() + 1, 0);
     for (size_t i = 0; i < hi.e_mult.size(); ++i) gcum[i + 1] = gcum[i] + hi.e_mult[i];
@@ -305,7 +327,9 @@ struct SeedWindow {
 __device__ __forceinline__ bool seed_lookup(const DevIndex &idx, int t, uint64_t code, int lo, int hi,
                                             SeedWindow &w) {
     const uint64_t *codes = idx.codes[t];
-    int a = 0, b = idx.ncodes[t];
+    const uint64_t pfx = code >> idx.lut_shift[t];
+    if (pfx >> VSK_LUT_BITS) return false;  // above every code of the index
+    int a = idx.lut[t][pfx], b = idx.lut[t][pfx + 1];
     while (a < b) {
         const int m = (a + b) >> 1;
         if (codes[m] < code) a = m + 1;
