@@ -238,6 +238,24 @@ int vsk_clusters_write(const vsk_link *links, int64_t n, const char *clu_path, c
 int vsk_clusters_write_r(const vsk_link *links, int64_t n, const char *clu_path, const char *map_path,
                          uint64_t *trcount);
 
+/* ---- join_clusters -------------------------------------------------------------------
+ * The merge of the per-file PROCLU cluster files into one file (reference
+ * src/join_clusters/joinc.c:128-391, loader :393-571): clusters that share a reference TR
+ * (negative id) are chained together, the absorbed chain flipped when the two disagree on
+ * that reference's direction; output = the reference's bytes (member order included).
+ * Host code, no vsk_ctx and no GPU needed.  `paths` are sorted by strcmp as the reference
+ * sorts its file list; vsk_join_clusters_dir takes the folder and picks the files the
+ * reference picks (names longer than 6 characters ending in ".clu", any case).
+ * Errors on which the reference exit(1)s give VSK_ERR_ABORT with its message in `err`.   */
+typedef struct {
+    int32_t clusters_read, clusters_after_join, maxdepth, pad_;
+    int64_t refs_read, refs_written, reads_read, reads_written;
+} vsk_join_stats;
+int vsk_join_clusters_files(const char *const *paths, int32_t n_paths, const char *out_path,
+                            vsk_join_stats *stats, char *err, size_t errlen);
+int vsk_join_clusters_dir(const char *dir, const char *out_path, vsk_join_stats *stats, int verbose,
+                          char *err, size_t errlen);
+
 /* ---- flankalign ---------------------------------------------------------------------
  * vsk_flankalign_run = the whole of flankalign.exe after argv (reference
  * src/newflankalign/flankalign.c:288-823): parse the `.flanks` blocks, order reads and

@@ -78,6 +78,12 @@ class ProcluStats(C.Structure):
                 ("dp_alg_bytes", C.c_int64)]
 
 
+class JoinStats(C.Structure):
+    _fields_ = [("clusters_read", C.c_int32), ("clusters_after_join", C.c_int32), ("maxdepth", C.c_int32),
+                ("pad_", C.c_int32), ("refs_read", C.c_int64), ("refs_written", C.c_int64),
+                ("reads_read", C.c_int64), ("reads_written", C.c_int64)]
+
+
 LINK_DTYPE = np.dtype([("refkey", np.int32), ("readkey", np.int32), ("dir", np.int32),
                        ("lerr", np.int32), ("rerr", np.int32), ("dsum", np.int32), ("sumw", np.int32)])
 
@@ -114,6 +120,10 @@ def _declare2(L):
     L.vsk_proclu_result_free.argtypes = [vp]
     L.vsk_proclu_result_free.restype = None
     L.vsk_clusters_write.argtypes = [vp, C.c_int64, C.c_char_p, C.c_char_p, C.POINTER(C.c_uint64)]
+    L.vsk_join_clusters_files.argtypes = [C.POINTER(C.c_char_p), C.c_int32, C.c_char_p, C.POINTER(JoinStats),
+                                          C.c_char_p, C.c_size_t]
+    L.vsk_join_clusters_dir.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(JoinStats), C.c_int, C.c_char_p,
+                                        C.c_size_t]
     L.vsk_timer_start.argtypes = [vp]
     L.vsk_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
     L.vsk_profile_enable.argtypes = [vp, C.c_int]

@@ -1,6 +1,7 @@
 """Thin Python mirror of the libvsk C ABI (include/vsk.h).  Every call goes
 through the shared library; nothing here computes alignment results."""
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -309,6 +310,22 @@ def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=T
         links = np.zeros(0, LINK_DTYPE)
     lib().vsk_proclu_result_free(res)
     return links, _stats_dict(st)
+
+
+def join_clusters(src, out_path):
+    """vsk_join_clusters_dir (src = a folder) or vsk_join_clusters_files (src = a list of .clu
+    paths): the reference's join_clusters merge.  Host only, no Context.  Returns the counters."""
+    from ._lib import JoinStats
+    st = JoinStats()
+    err = C.create_string_buffer(600)
+    if isinstance(src, (str, bytes, os.PathLike)):
+        rc = lib().vsk_join_clusters_dir(os.fsencode(src), os.fsencode(out_path), C.byref(st), 0, err, len(err))
+    else:
+        arr = (C.c_char_p * len(src))(*[os.fsencode(p) for p in src])
+        rc = lib().vsk_join_clusters_files(arr, len(src), os.fsencode(out_path), C.byref(st), err, len(err))
+    if rc != 0:
+        raise VskError(f"join_clusters failed ({rc}): {err.value.decode()}")
+    return {name: int(getattr(st, name)) for name, _ in JoinStats._fields_ if name != "pad_"}
 
 
 def write_clusters(links, clu_path, map_path=None):
