@@ -256,6 +256,19 @@ int vsk_join_clusters_files(const char *const *paths, int32_t n_paths, const cha
 int vsk_join_clusters_dir(const char *dir, const char *out_path, vsk_join_stats *stats, int verbose,
                           char *err, size_t errlen);
 
+/* ---- best-reference table ------------------------------------------------------------
+ * What perl/run_rankflankmap.pl:96-231 computes from flankalign's .map files before it
+ * talks to the database: per read line the hits `ref:lerr:rerr` score
+ * 1-(lerr+rerr)/(leftlen+rightlen) (0 for a read without flanks), hits under 0.90 are
+ * dropped, the best score wins, ties are kept.  rank_tsv gets the rows of its `rankflank`
+ * table (refid, readid, score printed %.15g as Perl prints it, ties), map_tsv (may be
+ * NULL) those of its `map` table (refid, readid); files of the folder whose names do not
+ * start with "_map", in name order.  Host code, no vsk_ctx.                             */
+typedef struct {
+    int64_t files, read_lines, map_rows, rank_rows, reads_ranked;
+} vsk_rank_stats;
+int vsk_rankflank_dir(const char *mapdir, const char *rank_tsv, const char *map_tsv, vsk_rank_stats *stats);
+
 /* ---- flankalign ---------------------------------------------------------------------
  * vsk_flankalign_run = the whole of flankalign.exe after argv (reference
  * src/newflankalign/flankalign.c:288-823): parse the `.flanks` blocks, order reads and

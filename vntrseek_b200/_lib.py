@@ -84,6 +84,11 @@ class JoinStats(C.Structure):
                 ("reads_read", C.c_int64), ("reads_written", C.c_int64)]
 
 
+class RankStats(C.Structure):
+    _fields_ = [("files", C.c_int64), ("read_lines", C.c_int64), ("map_rows", C.c_int64),
+                ("rank_rows", C.c_int64), ("reads_ranked", C.c_int64)]
+
+
 LINK_DTYPE = np.dtype([("refkey", np.int32), ("readkey", np.int32), ("dir", np.int32),
                        ("lerr", np.int32), ("rerr", np.int32), ("dsum", np.int32), ("sumw", np.int32)])
 
@@ -122,6 +127,7 @@ def _declare2(L):
     L.vsk_clusters_write.argtypes = [vp, C.c_int64, C.c_char_p, C.c_char_p, C.POINTER(C.c_uint64)]
     L.vsk_join_clusters_files.argtypes = [C.POINTER(C.c_char_p), C.c_int32, C.c_char_p, C.POINTER(JoinStats),
                                           C.c_char_p, C.c_size_t]
+    L.vsk_rankflank_dir.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(RankStats)]
     L.vsk_join_clusters_dir.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(JoinStats), C.c_int, C.c_char_p,
                                         C.c_size_t]
     L.vsk_timer_start.argtypes = [vp]

@@ -328,6 +328,18 @@ def join_clusters(src, out_path):
     return {name: int(getattr(st, name)) for name, _ in JoinStats._fields_ if name != "pad_"}
 
 
+def rankflank(mapdir, rank_tsv, map_tsv=None):
+    """vsk_rankflank_dir: best-reference rows (refid, readid, score, ties) from flankalign's .map
+    files, and optionally the (refid, readid) rows of every hit.  Host only.  Returns the counters."""
+    from ._lib import RankStats
+    st = RankStats()
+    rc = lib().vsk_rankflank_dir(os.fsencode(mapdir), os.fsencode(rank_tsv),
+                                 os.fsencode(map_tsv) if map_tsv else None, C.byref(st))
+    if rc != 0:
+        raise VskError(f"vsk_rankflank_dir failed ({rc})")
+    return {name: int(getattr(st, name)) for name, _ in RankStats._fields_}
+
+
 def write_clusters(links, clu_path, map_path=None):
     links = np.ascontiguousarray(links, LINK_DTYPE)
     tr = C.c_uint64()
