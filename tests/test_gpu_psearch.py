@@ -66,6 +66,44 @@ def test_psearch_very_long_patterns(tmp_path, dst_file, monkeypatch):
     assert canonical_clu(os.path.join(b, "reads.leb36.clu")) == canonical_clu(os.path.join(a, "reads.leb36.clu"))
 
 
+def _canonical_joined(path):
+    """all.clusters -> set of clusters, each a frozenset of (id, dir) with the smallest id's mark normalised"""
+    out = set()
+    for line in open(path):
+        mem = [(int(t[:-1]), t[-1]) for t in line.strip().split(",") if t]
+        flip = min(mem)[1] != "'"
+        out.add(frozenset((i, ("'" if (d == "'") != flip else '"')) for i, d in mem))
+    return out
+
+
+def test_sharded_psearch_then_join(tmp_path, dst_file):
+    """the multi-GPU shape of the step at file level: the reads in two files, one psearch run per
+    file, join_clusters over the two .clu -- ours end to end against the reference end to end"""
+    if not (_have_ref() and os.path.exists(os.path.join(REF_BIN, "join_clusters.exe"))):
+        pytest.skip("oracle/_ref binaries not built")
+    from vntrseek_b200 import synth
+    refs = synth.make_refs(500, seed=31, max_patlen=300, rot_frac=0.0)
+    reads = synth.make_reads(refs, 800, seed=131, rot_frac=0.0)
+    half = len(reads.key) // 2
+    outs = {}
+    for name, bindir in (("ref", REF_BIN), ("our", OUR_BIN)):
+        w = str(tmp_path / name)
+        os.makedirs(os.path.join(w, "clu"))
+        refs.write_leb36(os.path.join(w, "reference.leb36"))
+        for part, (a, b) in enumerate(((0, half), (half, len(reads.key)))):
+            reads.subset(range(a, b)).write_leb36(os.path.join(w, "reads%d.leb36" % part))
+            rc, _, log = run(os.path.join(bindir, "psearch.exe"),
+                             ["reference.leb36", "reads%d.leb36" % part, dst_file, 88, 0, 50], w)
+            assert rc == 0, log[-500:]
+            shutil.move(os.path.join(w, "reads%d.leb36.clu" % part), os.path.join(w, "clu"))
+        rc, out, _ = run(os.path.join(bindir, "join_clusters.exe"), ["clu", "all.clusters"], w)
+        assert rc == 0
+        outs[name] = (_canonical_joined(os.path.join(w, "all.clusters")), out.splitlines()[-1])
+    assert len(outs["ref"][0]) > 20
+    assert outs["our"][0] == outs["ref"][0]
+    assert outs["our"][1] == outs["ref"][1]  # the summary line: clusters read / after join / refs / reads
+
+
 def test_psearch_golden_small(tmp_path, dst_file):
     """committed fixture (inputs + the reference's outputs), no reference binary needed"""
     from conftest import GOLDEN
