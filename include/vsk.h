@@ -185,6 +185,17 @@ typedef struct vsk_refs vsk_refs;
 typedef struct vsk_reads vsk_reads;
 typedef struct vsk_proclu_result vsk_proclu_result;
 int vsk_refs_create(vsk_ctx *ctx, const vsk_trset *refs, vsk_refs **out);
+/* The same with the flattened index kept in a file.  The reference rebuilds its index in every
+ * psearch process (psearch.c:507-766); here the build is ~48 s of serial host work for 250 K
+ * references (its sort order has to be replayed for the one-hit-beyond-`hi` rule), and every
+ * process of a run uses the same reference file.  cache_path (NULL = no cache): read when it
+ * holds the index of exactly this reference set (fingerprint of record count, pattern lengths,
+ * master flags after the rotindex, consensus strings), else the index is built and the file
+ * written through a temporary + rename.  vsk_index_cache_build does the host part alone (e.g.
+ * once at install time, no GPU needed); vsk_index_cache_verify rebuilds and compares.        */
+int vsk_refs_create_cached(vsk_ctx *ctx, const vsk_trset *refs, const char *cache_path, vsk_refs **out);
+int vsk_index_cache_build(const vsk_trset *refs, const char *path, int *from_cache);
+int vsk_index_cache_verify(const vsk_trset *refs, const char *path);
 void vsk_refs_free(vsk_ctx *ctx, vsk_refs *refs);
 int64_t vsk_refs_seed_hits(const vsk_refs *refs);
 

@@ -139,6 +139,38 @@ def test_alternative_paths_give_the_same_files(tmp_path, dst_file, switch):
     assert outs[0][0] == parse_counters(open(os.path.join(g, "ref.log")).read())
 
 
+def test_index_cache_same_output(tmp_path, dst_file):
+    """VSK_INDEX_CACHE=1: the first run writes <REFPROFILES>.vskidx, the second reads it, a damaged
+    file is ignored -- counters and .clu are those of a run without the cache every time"""
+    from conftest import GOLDEN
+    g = os.path.join(GOLDEN, "psearch_small")
+    want = None
+    for step in ("plain", "write", "read", "damaged"):
+        w = str(tmp_path / step)
+        shutil.copytree(g, w)
+        os.remove(os.path.join(w, "reads.leb36.clu"))
+        env = dict(os.environ)
+        idx = os.path.join(w, "reference.leb36.vskidx")
+        if step != "plain":
+            env["VSK_INDEX_CACHE"] = "1"
+        if step == "read":
+            shutil.copy(str(tmp_path / "write" / "reference.leb36.vskidx"), idx)
+            before = os.path.getmtime(idx)
+        if step == "damaged":
+            open(idx, "wb").write(open(str(tmp_path / "write" / "reference.leb36.vskidx"), "rb").read()[:5000])
+        rc, _, log = run(os.path.join(OUR_BIN, "psearch.exe"), ["reference.leb36", "reads.leb36", dst_file, 88, 0, 50], w,
+                         env=env)
+        assert rc == 0, log[-500:]
+        got = (parse_counters(log), open(os.path.join(w, "reads.leb36.clu")).read())
+        want = want or got
+        assert got == want, step
+        assert os.path.exists(idx) == (step != "plain")
+        if step == "read":
+            assert os.path.getmtime(idx) == before   # used, not rewritten
+        if step == "damaged":
+            assert os.path.getsize(idx) > 5000       # replaced by a good one
+
+
 def test_edges_mode_byte_exact(tmp_path, dst_file):
     if not _have_ref():
         pytest.skip("oracle/_ref/psearch.exe not built")

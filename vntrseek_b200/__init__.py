@@ -5,4 +5,5 @@ The product is the C-ABI library `libvsk.so` (include/vsk.h) plus the drop-in
 is a thin ctypes mirror of that ABI used by the tests and bench.py.
 """
 from .api import (Context, ProfileSet, RefIndex, ResidentReads, TRSetHandle, VskError, pack_profiles,  # noqa: F401
-                  pack_strings, join_clusters, proclu, rankflank, write_clusters)
+                  pack_strings, index_cache_build, index_cache_verify, join_clusters, proclu, rankflank,
+                  write_clusters)

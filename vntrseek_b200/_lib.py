@@ -109,6 +109,9 @@ def _declare2(L):
     L.vsk_trset_free.argtypes = [vp]
     L.vsk_trset_free.restype = None
     L.vsk_refs_create.argtypes = [vp, vp, C.POINTER(vp)]
+    L.vsk_refs_create_cached.argtypes = [vp, vp, C.c_char_p, C.POINTER(vp)]
+    L.vsk_index_cache_build.argtypes = [vp, C.c_char_p, C.POINTER(C.c_int)]
+    L.vsk_index_cache_verify.argtypes = [vp, C.c_char_p]
     L.vsk_refs_free.argtypes = [vp, vp]
     L.vsk_refs_free.restype = None
     L.vsk_refs_seed_hits.argtypes = [vp]

@@ -242,10 +242,11 @@ class TRSetHandle:
 class RefIndex:
     """vsk_refs: reference TR set + seed index resident in HBM."""
 
-    def __init__(self, ctx, trset):
+    def __init__(self, ctx, trset, cache_path=None):
         self.ctx, self.trset = ctx, trset
         self.h = C.c_void_p()
-        ctx._check(lib().vsk_refs_create(ctx.h, trset.h, C.byref(self.h)))
+        ctx._check(lib().vsk_refs_create_cached(ctx.h, trset.h, os.fsencode(cache_path) if cache_path else None,
+                                                C.byref(self.h)))
 
     @property
     def seed_hits(self):
@@ -310,6 +311,21 @@ def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=T
         links = np.zeros(0, LINK_DTYPE)
     lib().vsk_proclu_result_free(res)
     return links, _stats_dict(st)
+
+
+def index_cache_build(trset, path):
+    """vsk_index_cache_build: make sure `path` holds the seed index of this reference set (host only).
+    Returns True when the file was already good."""
+    hit = C.c_int(0)
+    rc = lib().vsk_index_cache_build(trset.h, os.fsencode(path), C.byref(hit))
+    if rc != 0:
+        raise VskError(f"vsk_index_cache_build failed ({rc})")
+    return bool(hit.value)
+
+
+def index_cache_verify(trset, path):
+    """vsk_index_cache_verify: True when the file holds this set's index and equals a fresh build"""
+    return lib().vsk_index_cache_verify(trset.h, os.fsencode(path)) == 0
 
 
 def join_clusters(src, out_path):

@@ -144,7 +144,21 @@ int main(int argc, char **argv) {
         int64_t nl;
         uint64_t trcount = 0;
         fprintf(stderr, "\nSeeding reference profiles' concensus sequences...");
-        if (vsk_refs_create(ctx, refs, &R) != VSK_OK) die(vsk_last_error(ctx));
+        {   /* VSK_INDEX_CACHE: unset = build the index in this process; "1" = keep it in
+               <REFPROFILES>.vskidx; anything else = that file */
+            const char *ic = getenv("VSK_INDEX_CACHE");
+            char icpath[1200];
+            const char *cache = NULL;
+            if (ic && *ic && strcmp(ic, "0") != 0) {
+                if (0 == strcmp(ic, "1")) {
+                    snprintf(icpath, sizeof icpath, "%s.vskidx", argv[1]);
+                    cache = icpath;
+                } else {
+                    cache = ic;
+                }
+            }
+            if (vsk_refs_create_cached(ctx, refs, cache, &R) != VSK_OK) die(vsk_last_error(ctx));
+        }
         fprintf(stderr, "(total time: %.1lf secs)", (double) (time(NULL) - startTime));
         fprintf(stderr, "\nScanning reads...");
         memset(&prm, 0, sizeof prm);

@@ -63,6 +63,9 @@ struct vsk_refindex_host {
 };
 
 int vsk_build_refindex_host(const vsk_trset &refs, vsk_refindex_host &out, std::string &err);
+// the same through the on-disk cache (vsk_index.cu, "index cache"); cache_path may be null
+int vsk_refindex_get(const vsk_trset &refs, const char *cache_path, vsk_refindex_host &hi, std::string &err,
+                     int *from_cache);
 
 // accepted link, in the order psearch would have called ClusterBaseAddLink
 struct vsk_link_rec {

@@ -13,6 +13,7 @@
 // survives into the device index; the rest of a bucket is a set.
 #include <math.h>
 #include <string.h>
+#include <unistd.h>
 
 #include <algorithm>
 
@@ -386,4 +387,143 @@ int vsk_build_refindex_host(const vsk_trset &refs, vsk_refindex_host &out, std::
         out.bucket_off[t].push_back((int64_t)out.e_prof.size());
     }
     return VSK_OK;
+}
+
+// ---- index cache ------------------------------------------------------------------------
+// The index is a function of the reference set alone, and building it is serial host work (the
+// reference's own sort has to be replayed hit by hit, see the top of this file): ~48 s for 250 K
+// references, paid by every psearch process although all of them use the same reference file.
+// vsk_refs_create_cached keeps the flattened index in a file next to wherever the caller wants it:
+// magic, version, a fingerprint of everything the build reads (number of records, pattern
+// lengths, master flags, consensus strings), the arrays, an end mark.  A file that does not
+// match in any of these is ignored and rewritten (temporary file + rename, so concurrent
+// processes never see a partial one).
+static const char kIdxMagic[8] = {'V', 'S', 'K', 'I', 'D', 'X', '2', 0};
+static const uint64_t kIdxEnd = 0x58444e4549444e45ull;
+
+static uint64_t fp_mix(uint64_t h, const void *data, size_t bytes) {
+    const uint8_t *p = (const uint8_t *)data;
+    size_t i = 0;
+    for (; i + 8 <= bytes; i += 8) {
+        uint64_t w;
+        memcpy(&w, p + i, 8);
+        h = (h ^ w) * 0x9e3779b97f4a7c15ull;
+        h ^= h >> 29;
+    }
+    for (; i < bytes; ++i) h = (h ^ p[i]) * 0x100000001b3ull;
+    return h;
+}
+
+uint64_t vsk_refs_fingerprint(const vsk_trset &refs) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    const int64_t n = refs.n;
+    h = fp_mix(h, &n, sizeof n);
+    h = fp_mix(h, refs.patlen.data(), refs.patlen.size() * sizeof(int32_t));
+    h = fp_mix(h, refs.master.data(), refs.master.size());
+    h = fp_mix(h, refs.cons_off.data(), refs.cons_off.size() * sizeof(int64_t));
+    h = fp_mix(h, refs.cons.data(), refs.cons.size());
+    return h;
+}
+
+template <typename T>
+static bool put_vec(FILE *f, const std::vector<T> &v) {
+    const uint64_t n = v.size();
+    if (fwrite(&n, sizeof n, 1, f) != 1) return false;
+    return n == 0 || fwrite(v.data(), sizeof(T), n, f) == n;
+}
+
+template <typename T>
+static bool get_vec(FILE *f, std::vector<T> &v, uint64_t limit) {
+    uint64_t n = 0;
+    if (fread(&n, sizeof n, 1, f) != 1 || n > limit) return false;
+    v.resize(n);
+    return n == 0 || fread(v.data(), sizeof(T), n, f) == n;
+}
+
+int vsk_refindex_save(const vsk_refindex_host &hi, uint64_t fingerprint, const char *path) {
+    const std::string tmp = std::string(path) + ".tmp" + std::to_string((long long)getpid());
+    FILE *f = fopen(tmp.c_str(), "wb");
+    if (!f) return VSK_ERR_ARG;
+    bool ok = fwrite(kIdxMagic, 8, 1, f) == 1 && fwrite(&fingerprint, 8, 1, f) == 1 &&
+              fwrite(&hi.total_hits, 8, 1, f) == 1 && fwrite(&hi.tuples, 8, 1, f) == 1;
+    for (int t = 1; t <= 14 && ok; ++t) ok = put_vec(f, hi.codes[t]) && put_vec(f, hi.bucket_off[t]);
+    ok = ok && put_vec(f, hi.e_pmin) && put_vec(f, hi.e_prof) && put_vec(f, hi.e_mult) && put_vec(f, hi.e_first) &&
+         put_vec(f, hi.e_cum) && fwrite(&kIdxEnd, 8, 1, f) == 1;
+    ok = (fclose(f) == 0) && ok;
+    if (!ok || rename(tmp.c_str(), path) != 0) {
+        remove(tmp.c_str());
+        return VSK_ERR_ARG;
+    }
+    return VSK_OK;
+}
+
+// VSK_OK = loaded; anything else = no usable file (absent, other reference set, truncated, older format)
+int vsk_refindex_load(vsk_refindex_host &hi, uint64_t fingerprint, const char *path) {
+    FILE *f = fopen(path, "rb");
+    if (!f) return VSK_ERR_ARG;
+    fseek(f, 0, SEEK_END);
+    const uint64_t limit = (uint64_t)ftell(f);  // no array can have more elements than the file has bytes
+    fseek(f, 0, SEEK_SET);
+    char magic[8];
+    uint64_t fp = 0, end = 0;
+    hi = vsk_refindex_host();
+    bool ok = fread(magic, 8, 1, f) == 1 && memcmp(magic, kIdxMagic, 8) == 0 && fread(&fp, 8, 1, f) == 1 &&
+              fp == fingerprint && fread(&hi.total_hits, 8, 1, f) == 1 && fread(&hi.tuples, 8, 1, f) == 1;
+    for (int t = 1; t <= 14 && ok; ++t) ok = get_vec(f, hi.codes[t], limit) && get_vec(f, hi.bucket_off[t], limit);
+    ok = ok && get_vec(f, hi.e_pmin, limit) && get_vec(f, hi.e_prof, limit) && get_vec(f, hi.e_mult, limit) &&
+         get_vec(f, hi.e_first, limit) && get_vec(f, hi.e_cum, limit) && fread(&end, 8, 1, f) == 1 && end == kIdxEnd;
+    fclose(f);
+    if (ok) {  // shape checks: the device code indexes these arrays without looking
+        const size_t ne = hi.e_prof.size();
+        ok = hi.e_pmin.size() == ne && hi.e_mult.size() == ne && hi.e_first.size() == ne && hi.e_cum.size() == ne;
+        for (int t = 1; t <= 14 && ok; ++t)
+            ok = hi.bucket_off[t].size() == hi.codes[t].size() + 1 || (hi.codes[t].empty() && hi.bucket_off[t].size() <= 1);
+    }
+    if (!ok) hi = vsk_refindex_host();
+    return ok ? VSK_OK : VSK_ERR_ARG;
+}
+
+// the index of `refs`: from `cache_path` when it holds this reference set's, else built (and the
+// file written; a failure to write is not an error).  *from_cache tells which.
+int vsk_refindex_get(const vsk_trset &refs, const char *cache_path, vsk_refindex_host &hi, std::string &err,
+                     int *from_cache) {
+    if (from_cache) *from_cache = 0;
+    uint64_t fp = 0;
+    if (cache_path && *cache_path) {
+        fp = vsk_refs_fingerprint(refs);
+        if (vsk_refindex_load(hi, fp, cache_path) == VSK_OK) {
+            if (from_cache) *from_cache = 1;
+            return VSK_OK;
+        }
+    }
+    const int rc = vsk_build_refindex_host(refs, hi, err);
+    if (rc) return rc;
+    if (cache_path && *cache_path) vsk_refindex_save(hi, fp, cache_path);
+    return VSK_OK;
+}
+
+extern "C" int vsk_index_cache_build(const vsk_trset *refs, const char *path, int *from_cache) {
+    if (!refs || !path || !*path) return VSK_ERR_ARG;
+    vsk_refindex_host hi;
+    std::string err;
+    return vsk_refindex_get(*refs, path, hi, err, from_cache);
+}
+
+// VSK_OK when `path` holds the index of `refs` and it equals, array by array, a fresh build
+extern "C" int vsk_index_cache_verify(const vsk_trset *refs, const char *path) {
+    if (!refs || !path) return VSK_ERR_ARG;
+    vsk_refindex_host a, b;
+    std::string err;
+    if (vsk_refindex_load(a, vsk_refs_fingerprint(*refs), path) != VSK_OK) return VSK_ERR_ARG;
+    const int rc = vsk_build_refindex_host(*refs, b, err);
+    if (rc) return rc;
+    bool same = a.total_hits == b.total_hits && a.tuples == b.tuples && a.e_pmin == b.e_pmin && a.e_prof == b.e_prof &&
+                a.e_mult == b.e_mult && a.e_first == b.e_first && a.e_cum == b.e_cum;
+    for (int t = 1; t <= 14 && same; ++t) {
+        std::vector<int64_t> x = a.bucket_off[t], y = b.bucket_off[t];
+        if (x.empty()) x.push_back(0);  // an unused TRANGE is stored either way
+        if (y.empty()) y.push_back(0);
+        same = a.codes[t] == b.codes[t] && (a.codes[t].empty() || x == y);
+    }
+    return same ? VSK_OK : VSK_ERR_ABORT;
 }

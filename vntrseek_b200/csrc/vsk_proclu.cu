@@ -218,12 +218,16 @@ extern "C" void vsk_reads_free(vsk_ctx *ctx, vsk_reads *r) {
 }
 
 extern "C" int vsk_refs_create(vsk_ctx *ctx, const vsk_trset *refs, vsk_refs **out) {
+    return vsk_refs_create_cached(ctx, refs, nullptr, out);
+}
+
+extern "C" int vsk_refs_create_cached(vsk_ctx *ctx, const vsk_trset *refs, const char *cache_path, vsk_refs **out) {
     if (!ctx || !refs || !out) return VSK_ERR_ARG;
     *out = nullptr;
     VSK_CUDA(ctx, cudaSetDevice(ctx->device));
     vsk_refindex_host hi;
     std::string err;
-    int rc = vsk_build_refindex_host(*refs, hi, err);
+    int rc = vsk_refindex_get(*refs, cache_path, hi, err, nullptr);
     if (rc) return vsk_fail(ctx, rc, "%s", err.c_str());
     vsk_refs *R = new vsk_refs();
     R->ctx = ctx;
