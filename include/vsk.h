@@ -173,6 +173,11 @@ int vsk_trsets_check_unique(const vsk_trset *a, const vsk_trset *b, int32_t *dup
 /* page-lock the set's large arrays (one-time) so vsk_proclu_run's H2D copies run at PCIe rate */
 int vsk_trset_pin(vsk_trset *ts);
 int32_t vsk_trset_size(const vsk_trset *ts);
+/* Diagnostic: order-sensitive hash of everything the set holds (records, profiles, consensus,
+ * flanks, redundancy state).  Large .leb36 files are parsed by several host threads
+ * (VSK_LOAD_THREADS, default = cores up to 16; 1 = the serial parser); equal checksums mean the
+ * two ways loaded the same set.                                                              */
+uint64_t vsk_trset_checksum(const vsk_trset *ts);
 const char *vsk_trset_error(const vsk_trset *ts);
 void vsk_trset_free(vsk_trset *ts);
 

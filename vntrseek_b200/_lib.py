@@ -108,6 +108,8 @@ def _declare2(L):
     L.vsk_trset_error.restype = C.c_char_p
     L.vsk_trset_free.argtypes = [vp]
     L.vsk_trset_free.restype = None
+    L.vsk_trset_checksum.argtypes = [vp]
+    L.vsk_trset_checksum.restype = C.c_uint64
     L.vsk_refs_create.argtypes = [vp, vp, C.POINTER(vp)]
     L.vsk_refs_create_cached.argtypes = [vp, vp, C.c_char_p, C.POINTER(vp)]
     L.vsk_index_cache_build.argtypes = [vp, C.c_char_p, C.POINTER(C.c_int)]

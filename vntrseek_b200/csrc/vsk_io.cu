@@ -7,6 +7,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+#include <thread>
+
 #include "vsk_host.hpp"
 #include "vsk_internal.cuh"
 
@@ -120,21 +123,13 @@ static vsk_trset *new_trset(bool is_read) {
     return ts;
 }
 
-extern "C" int vsk_trset_load_leb36(const char *path, int is_read, int maxflank, int option_r, int reflen,
-                                    vsk_trset **out) {
-    if (!path || !out) return VSK_ERR_ARG;
-    *out = nullptr;
-    FILE *fp = fopen(path, "rb");
-    if (!fp) return VSK_ERR_ARG;
-    fseek(fp, 0, SEEK_END);
-    const long sz = ftell(fp);
-    fseek(fp, 0, SEEK_SET);
-    std::vector<char> buf((size_t)sz + 1);
-    if (sz > 0 && fread(buf.data(), 1, (size_t)sz, fp) != (size_t)sz) { fclose(fp); return VSK_ERR_ARG; }
-    fclose(fp);
-    buf[(size_t)sz] = 0;
-    vsk_trset *ts = new_trset(is_read != 0);
-    char *p = buf.data();
+// Parses the records in [p, end) (*end == 0) into ts.  Returns VSK_OK or VSK_ERR_ARG (bad composition
+// id, message in ts.err).  `stopped` = the range did not parse to its end (the reference stops at the
+// first record it cannot parse, psearch.c:332-345); `ragged` = a record was not on one line or the
+// range ended inside a record, i.e. line starts are not record starts in this file.
+static int parse_leb36_range(char *p, const char *path, int maxflank, bool option_r, int reflen, vsk_trset &ts,
+                             bool &stopped, bool &ragged) {
+    stopped = ragged = false;
     auto next_token = [&](char *&tok, size_t &len) -> bool {
         while (*p && isspace((unsigned char)*p)) ++p;
         if (!*p) return false;
@@ -144,12 +139,17 @@ extern "C" int vsk_trset_load_leb36(const char *path, int is_read, int maxflank,
         return true;
     };
     std::vector<uint16_t> fwd, rc;
-    for (;;) {  // the reference stops at the first record it cannot parse (psearch.c:332-345)
+    for (;;) {
         char *tok[12];
         size_t len[12];
-        bool ok = true;
-        for (int k = 0; k < 12 && ok; ++k) ok = next_token(tok[k], len[k]);
-        if (!ok) break;
+        int got = 0;
+        while (got < 12 && next_token(tok[got], len[got])) ++got;
+        if (got < 12) {
+            if (got > 0) stopped = ragged = true;  // the text ends inside a record
+            break;
+        }
+        if (memchr(tok[0], '\n', (size_t)(tok[11] + len[11] - tok[0]))) ragged = true;
+        stopped = true;  // until this record is accepted
         char *e;
         const long key = strtol(tok[0], &e, 10);
         if (e == tok[0]) break;
@@ -175,16 +175,112 @@ extern "C" int vsk_trset_load_leb36(const char *path, int is_read, int maxflank,
             rc[(size_t)i] = (uint16_t)v;
         }
         if (bad) {
-            ts->err = "composition id outside 0..1000 in " + std::string(path);
-            *out = ts;
+            ts.err = "composition id outside 0..1000 in " + std::string(path);
             return VSK_ERR_ARG;
         }
         // flanks token LEFT|RIGHT
         std::string fl(tok[11], len[11]);
         const size_t bar = fl.find('|');
         if (bar == std::string::npos) break;  // "No flanks specified!" -> NULL -> stop
-        finish_record(*ts, (int32_t)key, (int32_t)patlen, fwd, rc, fl.substr(0, bar), fl.substr(bar + 1),
-                      maxflank, option_r != 0, reflen);
+        finish_record(ts, (int32_t)key, (int32_t)patlen, fwd, rc, fl.substr(0, bar), fl.substr(bar + 1), maxflank,
+                      option_r, reflen);
+        stopped = false;
+    }
+    return VSK_OK;
+}
+
+// appends part b to a (offsets rebased)
+static void append_trset(vsk_trset &a, const vsk_trset &b) {
+    const int64_t id0 = (int64_t)a.ids.size(), c0 = (int64_t)a.cons.size(), f0 = (int64_t)a.fl.size();
+    a.key.insert(a.key.end(), b.key.begin(), b.key.end());
+    a.patlen.insert(a.patlen.end(), b.patlen.begin(), b.patlen.end());
+    a.ids.insert(a.ids.end(), b.ids.begin(), b.ids.end());
+    a.cons.insert(a.cons.end(), b.cons.begin(), b.cons.end());
+    a.fl.insert(a.fl.end(), b.fl.begin(), b.fl.end());
+    for (size_t i = 1; i < b.prof_off.size(); ++i) a.prof_off.push_back(b.prof_off[i] + id0);
+    for (size_t i = 1; i < b.cons_off.size(); ++i) a.cons_off.push_back(b.cons_off[i] + c0);
+    for (size_t i = 1; i < b.fl_off.size(); ++i) a.fl_off.push_back(b.fl_off[i] + f0);
+    a.leftlen.insert(a.leftlen.end(), b.leftlen.begin(), b.leftlen.end());
+    a.rightlen.insert(a.rightlen.end(), b.rightlen.begin(), b.rightlen.end());
+}
+
+extern "C" int vsk_trset_load_leb36(const char *path, int is_read, int maxflank, int option_r, int reflen,
+                                    vsk_trset **out) {
+    if (!path || !out) return VSK_ERR_ARG;
+    *out = nullptr;
+    FILE *fp = fopen(path, "rb");
+    if (!fp) return VSK_ERR_ARG;
+    fseek(fp, 0, SEEK_END);
+    const long sz = ftell(fp);
+    fseek(fp, 0, SEEK_SET);
+    std::vector<char> buf((size_t)sz + 1);
+    if (sz > 0 && fread(buf.data(), 1, (size_t)sz, fp) != (size_t)sz) { fclose(fp); return VSK_ERR_ARG; }
+    fclose(fp);
+    buf[(size_t)sz] = 0;
+    vsk_trset *ts = new_trset(is_read != 0);
+    // Text parsing is the slowest host step of a run once the scan is on the GPU (6 us per record on
+    // one core), so large files are cut at line starts and parsed by several threads, the parts
+    // joined in order.  That is the serial result when every record sits on its own line (what
+    // trf2proclu-ngs writes); a file where that does not hold is detected and parsed serially.
+    int nthreads = 1;
+    if (const char *e = getenv("VSK_LOAD_THREADS")) nthreads = atoi(e);
+    else if (sz > (4 << 20)) nthreads = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+    nthreads = (int)std::max<long>(1, std::min<long>(nthreads, sz / (1 << 20)));
+    bool done = false;
+    if (nthreads > 1) {
+        std::vector<char *> cut((size_t)nthreads + 1);
+        cut[0] = buf.data();
+        cut[(size_t)nthreads] = buf.data() + sz;
+        for (int k = 1; k < nthreads; ++k) {
+            char *q = buf.data() + (size_t)((double)sz * k / nthreads);
+            char *nl = (char *)memchr(q, '\n', (size_t)(buf.data() + sz - q));
+            cut[(size_t)k] = nl ? nl : buf.data() + sz;
+        }
+        std::vector<vsk_trset *> part((size_t)nthreads);
+        std::vector<int> rcs((size_t)nthreads, VSK_OK);
+        std::vector<char> stopped((size_t)nthreads, 0), ragged((size_t)nthreads, 0), saved((size_t)nthreads + 1, 0);
+        for (int k = 1; k <= nthreads; ++k) {  // a range ends in a NUL where its last newline was
+            saved[(size_t)k] = *cut[(size_t)k];
+            *cut[(size_t)k] = 0;
+        }
+        std::vector<std::thread> th;
+        for (int k = 0; k < nthreads; ++k)
+            th.emplace_back([&, k] {
+                part[(size_t)k] = new_trset(is_read != 0);
+                bool st = false, rg = false;
+                char *b = cut[(size_t)k] + (k > 0 && cut[(size_t)k] < buf.data() + sz ? 1 : 0);
+                if (b > cut[(size_t)k + 1]) b = cut[(size_t)k + 1];
+                rcs[(size_t)k] = parse_leb36_range(b, path, maxflank, option_r != 0, reflen, *part[(size_t)k], st, rg);
+                stopped[(size_t)k] = st;
+                ragged[(size_t)k] = rg;
+            });
+        for (auto &t : th) t.join();
+        bool any_ragged = false;
+        for (int k = 0; k < nthreads; ++k) any_ragged = any_ragged || ragged[(size_t)k];
+        if (!any_ragged) {
+            done = true;
+            for (int k = 0; k < nthreads; ++k) {
+                append_trset(*ts, *part[(size_t)k]);
+                if (rcs[(size_t)k] != VSK_OK) {
+                    ts->err = part[(size_t)k]->err;
+                    for (auto *q : part) delete q;
+                    *out = ts;
+                    return rcs[(size_t)k];
+                }
+                if (stopped[(size_t)k]) break;  // nothing after the first record that does not parse
+            }
+        }
+        for (auto *q : part) delete q;
+        if (!done)
+            for (int k = 1; k < nthreads; ++k) *cut[(size_t)k] = saved[(size_t)k];  // back to the text as read
+    }
+    if (!done) {
+        bool st, rg;
+        const int rc = parse_leb36_range(buf.data(), path, maxflank, option_r != 0, reflen, *ts, st, rg);
+        if (rc != VSK_OK) {
+            *out = ts;
+            return rc;
+        }
     }
     init_rot(*ts);
     *out = ts;
@@ -313,4 +409,33 @@ extern "C" int vsk_trsets_check_unique(const vsk_trset *a, const vsk_trset *b, i
             }
     }
     return VSK_OK;
+}
+
+// order-sensitive hash of everything a TR set holds (records, profiles, consensus, flanks, flank
+// lengths, redundancy state): two sets with the same value went through the loader the same way
+extern "C" uint64_t vsk_trset_checksum(const vsk_trset *ts) {
+    if (!ts) return 0;
+    uint64_t h = 0xcbf29ce484222325ull;
+    auto mix = [&](const void *d, size_t bytes) {
+        const uint8_t *p = (const uint8_t *)d;
+        for (size_t i = 0; i < bytes; ++i) h = (h ^ p[i]) * 0x100000001b3ull;
+        h ^= bytes;
+        h *= 0x9e3779b97f4a7c15ull;
+    };
+    const int64_t n = ts->n;
+    mix(&n, sizeof n);
+    mix(ts->key.data(), ts->key.size() * 4);
+    mix(ts->patlen.data(), ts->patlen.size() * 4);
+    mix(ts->prof_off.data(), ts->prof_off.size() * 8);
+    mix(ts->ids.data(), ts->ids.size() * 2);
+    mix(ts->cons_off.data(), ts->cons_off.size() * 8);
+    mix(ts->cons.data(), ts->cons.size());
+    mix(ts->fl_off.data(), ts->fl_off.size() * 8);
+    mix(ts->fl.data(), ts->fl.size());
+    mix(ts->leftlen.data(), ts->leftlen.size() * 4);
+    mix(ts->rightlen.data(), ts->rightlen.size() * 4);
+    mix(ts->master.data(), ts->master.size());
+    mix(ts->dir.data(), ts->dir.size());
+    for (const auto &r : ts->rotlist) mix(r.data(), r.size() * 4);
+    return h;
 }
