@@ -605,10 +605,10 @@ static int tiny_tables(vsk_ctx *ctx, const vsk_idset *ids, int *K_out) {
     return VSK_OK;
 }
 
-static int g_dp_attr_set = 0;
-static int g_tiny_attr_set = 0;
-
-static int g_q8_attr_set = 0;
+// kernel attributes are per device: one bit per device ordinal
+static uint64_t g_dp_attr_set = 0;
+static uint64_t g_tiny_attr_set = 0;
+static uint64_t g_q8_attr_set = 0;
 
 int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids,
                   const vsk_dp_job *d_jobs, int64_t n_jobs, int64_t n_q8, int64_t n_tiny, int32_t max_l1,
@@ -641,10 +641,10 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
     int64_t grid_w = 0;
     int stride_w = 0;
     if (n_warp > 0 || dir_any) {  // vsk_dp_kernel also takes the pairs the direction-bit path hands back
-        if (!g_dp_attr_set) {
+        if (!((g_dp_attr_set >> (ctx->device & 63)) & 1)) {
             VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                (int)DP_SMEM_BYTES));
-            g_dp_attr_set = 1;
+            g_dp_attr_set |= 1ull << (ctx->device & 63);
         }
         int per_sm = 0;
         VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_kernel, DP_WARPS * 32,
@@ -679,10 +679,10 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
     }
     if (n_q8 > 0 && !dir_q8) {
         const size_t smem = 2048 + 1024 + (size_t)K * K;
-        if (!g_q8_attr_set) {
+        if (!((g_q8_attr_set >> (ctx->device & 63)) & 1)) {
             VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_q8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                2048 + 1024 + 200 * 200));
-            g_q8_attr_set = 1;
+            g_q8_attr_set |= 1ull << (ctx->device & 63);
         }
         int per_sm = 0;
         VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_q8_kernel, Q8_WARPS * 32, smem));
@@ -700,11 +700,11 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
     if (n_tiny > 0) {
         const size_t smem = (size_t)(2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 + 2048 + 1024 +
                             (size_t)K * K;
-        if (!g_tiny_attr_set) {
+        if (!((g_tiny_attr_set >> (ctx->device & 63)) & 1)) {
             VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                (int)((2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 +
                                                      2048 + 1024 + 200 * 200)));
-            g_tiny_attr_set = 1;
+            g_tiny_attr_set |= 1ull << (ctx->device & 63);
         }
         vsk_dp_tiny_kernel<<<(unsigned)((n_tiny + TINY_THREADS - 1) / TINY_THREADS), TINY_THREADS, smem, ctx->stream>>>(
             d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,

@@ -673,7 +673,7 @@ __global__ void vsk_dd_bounds_kernel(const int64_t *__restrict__ off, int n, int
     bounds[b] = lo;
 }
 
-static int g_dd_attr_set = 0;
+static uint64_t g_dd_attr_set = 0;  // one bit per device ordinal
 
 int vsk_dp_dir_begin(vsk_ctx *ctx) {
     for (int i = 0; i < 2; ++i)
@@ -747,10 +747,10 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     const int64_t half_words = (nb == 1) ? total : batch_words + max_job_words;
     const int nhalf = nb == 1 ? 1 : 2;
 
-    if (!g_dd_attr_set) {
+    if (!((g_dd_attr_set >> (ctx->device & 63)) & 1)) {
         VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_dir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)DD_SMEM_BYTES));
-        g_dd_attr_set = 1;
+        g_dd_attr_set |= 1ull << (ctx->device & 63);
     }
     const size_t dd_smem = DD_SMEM_BYTES;
     int per_sm = 0;
@@ -762,11 +762,11 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     const size_t dq_smem = 2048 + DQ_WARPS * 32 * 64 + 1024 + (size_t)K * K;
     int grid8 = 0;
     if (n_q8 > 0) {
-        static int attr8 = 0;
-        if (!attr8) {
+        static uint64_t attr8 = 0;
+        if (!((attr8 >> (ctx->device & 63)) & 1)) {
             VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_q8dir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                2048 + DQ_WARPS * 32 * 64 + 1024 + 200 * 200));
-            attr8 = 1;
+            attr8 |= 1ull << (ctx->device & 63);
         }
         int per_sm8 = 0;
         VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm8, vsk_dp_q8dir_kernel, DQ_WARPS * 32, dq_smem));

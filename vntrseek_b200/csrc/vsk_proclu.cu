@@ -1011,11 +1011,11 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     int64_t npairs = 0;
     if (use_bitmap && bm_words <= 48000 && nprof < 0x7fffffff) {
         const size_t smem = (size_t)(bm_words + (bm_words + 31) / 32) * sizeof(uint32_t);
-        static int attr_set = 0;
-        if (!attr_set) {
+        static uint64_t attr_set = 0;  // one bit per device ordinal
+        if (!((attr_set >> (ctx->device & 63)) & 1)) {
             VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dedup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                (48000 + 1500) * (int)sizeof(uint32_t)));
-            attr_set = 1;
+            attr_set |= 1ull << (ctx->device & 63);
         }
         int per_sm = 0;
         VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dedup_kernel, DEDUP_THREADS, smem));
