@@ -168,8 +168,10 @@ int main(int argc, char **argv) {
         if (vsk_proclu_run(ctx, R, reads, &prm, &res) != VSK_OK) die(vsk_last_error(ctx));
         vsk_proclu_result_stats(res, &st);
         nl = vsk_proclu_result_links(res, &links);
-        rc = option_r ? vsk_clusters_write_r(links, nl, NULL, NULL, &trcount)
-                      : vsk_clusters_write(links, nl, NULL, NULL, &trcount);
+        /* the files are written before the counters block is printed (one pass over the links gives
+           both "total clustered" and the files); the block itself reads as the reference's */
+        rc = option_r ? vsk_clusters_write_r(links, nl, outputfile, option_m ? mapfile : NULL, &trcount)
+                      : vsk_clusters_write(links, nl, outputfile, option_m ? mapfile : NULL, &trcount);
         fprintf(stderr,
                 "\nscan finished!\n\t"
                 "CandidatesConsidered: %llu\n\t"
@@ -185,8 +187,6 @@ int main(int argc, char **argv) {
                 (unsigned long long) st.confirmed, (unsigned long long) trcount,
                 (double) (time(NULL) - startTime));
         fflush(stderr);
-        rc = option_r ? vsk_clusters_write_r(links, nl, outputfile, option_m ? mapfile : NULL, &trcount)
-                      : vsk_clusters_write(links, nl, outputfile, option_m ? mapfile : NULL, &trcount);
         if (rc != VSK_OK) {
             fprintf(stderr, "\nERROR: Unable to create output file '%s'", outputfile);
             exit(1);
