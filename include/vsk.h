@@ -51,6 +51,10 @@ int vsk_timer_stop(vsk_ctx *ctx, float *ms);
 int vsk_profile_enable(vsk_ctx *ctx, int on);
 int vsk_profile_read(vsk_ctx *ctx, double *dp_kernel_ms, int64_t *dp_kernel_launches);
 int vsk_int_peak(vsk_ctx *ctx, double *gops);
+/* profile mode: summed duration and number of launches of the forward-sweep kernel alone
+ * (vsk_dp_dir_kernel), events on the side stream each launch runs on.  Launches of consecutive
+ * batches overlap at their tails, so the sum can exceed the wall time of the DP stage.        */
+int vsk_profile_read_sweep(vsk_ctx *ctx, double *sweep_ms, int64_t *sweep_launches);
 /* profile mode: "stage=ms;..." of the PROCLU pipeline stages since the last call */
 int vsk_profile_stages(vsk_ctx *ctx, char *buf, size_t n);
 
@@ -209,7 +213,9 @@ typedef struct {
     int32_t maxerrors;   /* argv MAXERRORS, 0 = from flank length (hclust.h:660-668)  */
     int32_t option_r;    /* -r: ref-to-ref flank rules (hclust.h:700-751); needs maxerrors 0 */
     int32_t count_cells; /* 1: stats.dp_cells counts the reference's band cells exactly (slower) */
-    int64_t key_budget;  /* candidate keys per chunk, 0 = default                    */
+    int64_t key_budget;  /* candidate keys per chunk, 0 = default (or $VSK_KEY_BUDGET)  */
+    int32_t links_on_device; /* 1: the links stay in HBM only (vsk_proclu_result_links_dev), no D2H */
+    int32_t reserved_;
 } vsk_proclu_params;
 
 typedef struct {                          /* BLASTSTATS, hclust.h:43-51 */
@@ -223,6 +229,8 @@ typedef struct {                          /* BLASTSTATS, hclust.h:43-51 */
     int64_t chunks;
     int64_t h2d_bytes, d2h_bytes;
     int64_t dp_alg_bytes;                 /* sum over DP pairs of 2*(L1+L2)+16 bytes  */
+    int64_t dp_cells_sweep;               /* dp_cells of the pairs over 128 columns (forward-sweep kernel) */
+    int64_t dp_alg_bytes_sweep;           /* dp_alg_bytes of those pairs                                   */
 } vsk_proclu_stats;
 
 typedef struct {       /* one ClusterBaseAddLink call (hclust.h:813-822), in call order */
@@ -241,6 +249,11 @@ void vsk_reads_free(vsk_ctx *ctx, vsk_reads *reads);
 int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *refs, const vsk_reads *reads,
                             const vsk_proclu_params *prm, vsk_proclu_result **out);
 int64_t vsk_proclu_result_links(const vsk_proclu_result *r, const vsk_link **links);
+/* The same table in HBM (a DEVICE pointer; it belongs to the context and is overwritten by the
+ * context's next run): the send buffer of the multi-GPU merge, so that the per-rank tables go
+ * from the kernel that compacts them straight into the all-gather (the analogue of join_clusters
+ * reading the per-file .clu, src/join_clusters/joinc.c:246-317) without a trip through the host. */
+int64_t vsk_proclu_result_links_dev(const vsk_proclu_result *r, const vsk_link **d_links);
 void vsk_proclu_result_stats(const vsk_proclu_result *r, vsk_proclu_stats *stats);
 /* The links live in page-locked memory owned by the context: free every result before vsk_destroy. */
 void vsk_proclu_result_free(vsk_proclu_result *r);

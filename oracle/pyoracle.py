@@ -47,10 +47,51 @@ class Oracle:
         L.vo_flank_maxerr.argtypes = [C.c_int]
         L.vo_nbdist.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int]
         L.vo_band.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
+        _i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+        _u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+        L.vo_dp_batch.argtypes = [_u16p, _i64p, _u16p, _i64p, _i32p, _i32p, _u8p, C.c_int64, C.c_int, _i32p]
+        L.vo_dp_batch.restype = None
+        L.vo_lcs_batch.argtypes = [C.c_char_p, _i64p, C.c_char_p, _i64p, _i32p, _i32p, C.c_int64, _i32p]
+        L.vo_lcs_batch.restype = None
+        L.vo_ed_batch.argtypes = [C.c_char_p, _i64p, _i32p, C.c_char_p, _i64p, _i32p, C.c_int64, C.c_int, _i32p]
+        L.vo_ed_batch.restype = None
+        L.vo_nbdist_batch.argtypes = [C.c_char_p, _i64p, C.c_char_p, _i64p, C.c_int64, C.c_int, _i32p]
+        L.vo_nbdist_batch.restype = None
         self.L = L
         table = np.ascontiguousarray(table, dtype=np.uint8)
         assert table.size == 501501
         L.vo_init(table)
+
+    # batched forms (OpenMP over the pairs): same arithmetic, arrays in / arrays out
+    def dp_batch(self, loff, lids, toff, tids, li, ti, mode, homology=88):
+        li = np.ascontiguousarray(li, np.int32)
+        out = np.zeros((max(len(li), 1), 4), np.int32)
+        self.L.vo_dp_batch(np.ascontiguousarray(lids, np.uint16), np.ascontiguousarray(loff, np.int64),
+                           np.ascontiguousarray(tids, np.uint16), np.ascontiguousarray(toff, np.int64), li,
+                           np.ascontiguousarray(ti, np.int32), np.ascontiguousarray(mode, np.uint8), len(li),
+                           homology, out)
+        return out[:len(li)]
+
+    def lcs_batch(self, abuf, aoff, bbuf, boff, ia, ib):
+        ia = np.ascontiguousarray(ia, np.int32)
+        out = np.zeros(max(len(ia), 1), np.int32)
+        self.L.vo_lcs_batch(abuf, np.ascontiguousarray(aoff, np.int64), bbuf, np.ascontiguousarray(boff, np.int64),
+                            ia, np.ascontiguousarray(ib, np.int32), len(ia), out)
+        return out[:len(ia)]
+
+    def ed_batch(self, tbuf, toff, tlen, pbuf, poff, plen, variant):
+        n = len(tlen)
+        out = np.zeros(max(n, 1), np.int32)
+        self.L.vo_ed_batch(tbuf, np.ascontiguousarray(toff, np.int64), np.ascontiguousarray(tlen, np.int32), pbuf,
+                           np.ascontiguousarray(poff, np.int64), np.ascontiguousarray(plen, np.int32), n, variant, out)
+        return out[:n]
+
+    def nbdist_batch(self, abuf, aoff, bbuf, boff, maxerr):
+        n = len(aoff) - 1
+        out = np.zeros(max(n, 1), np.int32)
+        self.L.vo_nbdist_batch(abuf, np.ascontiguousarray(aoff, np.int64), bbuf, np.ascontiguousarray(boff, np.int64),
+                               n, maxerr, out)
+        return out[:n]
 
     def dp(self, left, top, mode=0, homology=88):
         left = np.ascontiguousarray(left, dtype=np.int32)
@@ -101,6 +142,11 @@ class Reference:
         for f in (L.ref_lcs, L.ref_ed_psearch, L.ref_ed_flankalign):
             f.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int]
         L.ref_nbdist.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int]
+        if hasattr(L, "ref_dp_batch"):
+            _i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+            _u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
+            L.ref_dp_batch.argtypes = [_u16p, _i64p, _u16p, _i64p, _i32p, _i32p, _u8p, C.c_int64, C.c_int, _i32p]
+            L.ref_dp_batch.restype = None
         self.L = L
         distfile = distfile or os.path.join(REF_DIR, "eucledian.dst")
         assert L.ref_init(distfile.encode()) == 0
@@ -111,6 +157,16 @@ class Reference:
         out = np.zeros(4, np.int32)
         sim = self.L.ref_dp(left, len(left), top, len(top), mode, homology, out)
         return tuple(int(x) for x in out), sim
+
+    def dp_batch(self, loff, lids, toff, tids, li, ti, mode, homology=88):
+        """the unmodified reference aligners over a pair list, the loop in C (one thread)"""
+        li = np.ascontiguousarray(li, np.int32)
+        out = np.zeros((max(len(li), 1), 4), np.int32)
+        self.L.ref_dp_batch(np.ascontiguousarray(lids, np.uint16), np.ascontiguousarray(loff, np.int64),
+                            np.ascontiguousarray(tids, np.uint16), np.ascontiguousarray(toff, np.int64), li,
+                            np.ascontiguousarray(ti, np.int32), np.ascontiguousarray(mode, np.uint8), len(li),
+                            homology, out)
+        return out[:len(li)]
 
     def lcs(self, s1, s2):
         return self.L.ref_lcs(s1, s2, len(s1), len(s2))

@@ -122,3 +122,21 @@ int ref_nbdist( const char *s1, const char *s2, int l1, int l2, int maxerr ) {
 }
 int ref_nondashes( int id ) { return NONDASHES[id]; }
 int ref_evaldistance( int r, int c ) { return EVALDISTANCE( r, c, g_sm ); }
+
+/* n pairs in one call (the loop in C, one thread): ids as uint16 with offsets, pair k =
+ * (left profile li[k], top profile ti[k]); out[4k..4k+3] as ref_dp */
+void ref_dp_batch( const unsigned short *lids, const long long *loff, const unsigned short *tids,
+  const long long *toff, const int *li, const int *ti, const unsigned char *mode, long long n,
+  int homology, int *out ) {
+    long long k;
+    for ( k = 0; k < n; k++ ) {
+        int  l1 = (int) ( loff[li[k] + 1] - loff[li[k]] ), l2 = (int) ( toff[ti[k] + 1] - toff[ti[k]] ), i;
+        int *a = (int *) malloc( sizeof( int ) * ( l1 + l2 + 2 ) ), *b = a + l1 + 1;
+        for ( i = 0; i < l1; i++ )
+            a[i] = lids[loff[li[k]] + i];
+        for ( i = 0; i < l2; i++ )
+            b[i] = tids[toff[ti[k]] + i];
+        ref_dp( a, l1, b, l2, mode[k], homology, out + 4 * k );
+        free( a );
+    }
+}

@@ -424,3 +424,119 @@ int vo_nbdist( const char *s1, const char *s2, int len1, int len2, int maxerr ) 
     free( cur );
     return score;
 }
+
+/* ---- batched forms of the functions above (arrays in, arrays out; pthreads over the pairs) ----
+ * Same arithmetic, one call per pair; they exist so that the kernel-level parity tests can
+ * check >= 10^6 pairs per kernel in seconds.                      */
+#include <pthread.h>
+#include <unistd.h>
+
+typedef struct {
+    void ( *fn )( int64_t k, void *arg );
+    void *   arg;
+    int64_t  n, chunk;
+    int64_t *next;
+} vo_pf;
+
+static void *vo_pf_worker( void *p ) {
+    vo_pf *w = (vo_pf *) p;
+    for ( ;; ) {
+        int64_t k0 = __atomic_fetch_add( w->next, w->chunk, __ATOMIC_RELAXED ), k;
+        if ( k0 >= w->n )
+            break;
+        for ( k = k0; k < w->n && k < k0 + w->chunk; k++ )
+            w->fn( k, w->arg );
+    }
+    return NULL;
+}
+
+static void vo_parallel_for( int64_t n, int64_t chunk, void ( *fn )( int64_t, void * ), void *arg ) {
+    long      nc = sysconf( _SC_NPROCESSORS_ONLN );
+    int       nt = (int) ( nc < 1 ? 1 : nc > 64 ? 64 : nc ), i;
+    int64_t   next = 0;
+    vo_pf     w    = { fn, arg, n, chunk, &next };
+    pthread_t th[64];
+    if ( n < 4 * chunk )
+        nt = 1;
+    for ( i = 1; i < nt; i++ )
+        if ( pthread_create( &th[i], NULL, vo_pf_worker, &w ) != 0 ) {
+            nt = i;
+            break;
+        }
+    vo_pf_worker( &w );
+    for ( i = 1; i < nt; i++ )
+        pthread_join( th[i], NULL );
+}
+
+typedef struct {
+    const uint16_t *lids, *tids;
+    const int64_t * loff, *toff;
+    const int32_t * li, *ti;
+    const uint8_t * mode;
+    int             homology;
+    int32_t *       out;
+} vo_dpb;
+
+static void vo_dp_one( int64_t k, void *p ) {
+    vo_dpb * q  = (vo_dpb *) p;
+    int      l1 = (int) ( q->loff[q->li[k] + 1] - q->loff[q->li[k]] );
+    int      l2 = (int) ( q->toff[q->ti[k] + 1] - q->toff[q->ti[k]] ), i;
+    int32_t *a = (int32_t *) malloc( sizeof( int32_t ) * ( l1 + l2 + 2 ) ), *b = a + l1 + 1;
+    for ( i = 0; i < l1; i++ )
+        a[i] = q->lids[q->loff[q->li[k]] + i];
+    for ( i = 0; i < l2; i++ )
+        b[i] = q->tids[q->toff[q->ti[k]] + i];
+    if ( vo_dp( a, l1, b, l2, q->mode[k], q->homology, q->out + 4 * k ) != 0 )
+        q->out[4 * k] = q->out[4 * k + 1] = q->out[4 * k + 2] = q->out[4 * k + 3] = -1;
+    free( a );
+}
+
+void vo_dp_batch( const uint16_t *lids, const int64_t *loff, const uint16_t *tids,
+  const int64_t *toff, const int32_t *li, const int32_t *ti, const uint8_t *mode, int64_t n,
+  int homology, int32_t *out ) {
+    vo_dpb q = { lids, tids, loff, toff, li, ti, mode, homology, out };
+    vo_parallel_for( n, 64, vo_dp_one, &q );
+}
+
+typedef struct {
+    const char *   a, *b;
+    const int64_t *aoff, *boff;
+    const int32_t *ia, *ib, *alen, *blen;
+    int            par;
+    int32_t *      out;
+} vo_strb;
+
+static void vo_lcs_one( int64_t k, void *p ) {
+    vo_strb *q = (vo_strb *) p;
+    q->out[k]  = vo_lcs( q->a + q->aoff[q->ia[k]], q->b + q->boff[q->ib[k]],
+      (int) ( q->aoff[q->ia[k] + 1] - q->aoff[q->ia[k]] ), (int) ( q->boff[q->ib[k] + 1] - q->boff[q->ib[k]] ) );
+}
+
+void vo_lcs_batch( const char *a, const int64_t *aoff, const char *b, const int64_t *boff,
+  const int32_t *ia, const int32_t *ib, int64_t n, int32_t *out ) {
+    vo_strb q = { a, b, aoff, boff, ia, ib, NULL, NULL, 0, out };
+    vo_parallel_for( n, 256, vo_lcs_one, &q );
+}
+
+static void vo_ed_one( int64_t k, void *p ) {
+    vo_strb *q = (vo_strb *) p;
+    q->out[k]  = vo_ed( q->a + q->aoff[k], q->b + q->boff[k], q->alen[k], q->blen[k], q->par );
+}
+
+void vo_ed_batch( const char *text, const int64_t *toff, const int32_t *tlen, const char *pat,
+  const int64_t *poff, const int32_t *plen, int64_t n, int variant, int32_t *out ) {
+    vo_strb q = { text, pat, toff, poff, NULL, NULL, tlen, plen, variant, out };
+    vo_parallel_for( n, 256, vo_ed_one, &q );
+}
+
+static void vo_nb_one( int64_t k, void *p ) {
+    vo_strb *q = (vo_strb *) p;
+    q->out[k]  = vo_nbdist( q->a + q->aoff[k], q->b + q->boff[k], (int) ( q->aoff[k + 1] - q->aoff[k] ),
+      (int) ( q->boff[k + 1] - q->boff[k] ), q->par );
+}
+
+void vo_nbdist_batch( const char *a, const int64_t *aoff, const char *b, const int64_t *boff, int64_t n,
+  int maxerr, int32_t *out ) {
+    vo_strb q = { a, b, aoff, boff, NULL, NULL, NULL, NULL, maxerr, out };
+    vo_parallel_for( n, 256, vo_nb_one, &q );
+}

@@ -44,6 +44,40 @@ def _worker(rank, world, port, n, outdir):
     dist.destroy_process_group()
 
 
+def _worker_gatherer(rank, world, port, n, outdir):
+    import torch
+    import torch.distributed as dist
+
+    from vntrseek_b200.dist import LinkGatherer, shard_bounds
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    g = LinkGatherer("cpu", root=0)
+    full = _links(0, n, 7)
+    for rep, cut in enumerate((n, n // 3, n)):  # the buffers are re-used: a smaller table after a larger one
+        lo, hi = shard_bounds(cut, rank, world)
+        mine = full[lo:hi] if not (rank == 1 and cut == 1) else full[:0]
+        t = torch.from_numpy(np.ascontiguousarray(mine).view(np.int32).reshape(-1, 7).copy())
+        got = g.gather(t)
+        assert (got is None) == (rank != 0)
+        if rank == 0:
+            np.save(os.path.join(outdir, "g%d.npy" % rep), got)
+    recv, counts = g.gather(t, to_host=False)
+    assert sum(counts) == n and recv.shape[0] == world
+    dist.destroy_process_group()
+
+
+def test_link_gatherer_two_ranks(tmp_path):
+    """the device-resident merge (dist.LinkGatherer) run over gloo with host tensors: rank order,
+    ragged counts, buffer re-use; only the root receives the host copy"""
+    n = 2003
+    mp.spawn(_worker_gatherer, args=(2, _free_port(), n, str(tmp_path)), nprocs=2, join=True)
+    full = _links(0, n, 7)
+    for rep, cut in enumerate((n, n // 3, n)):
+        got = np.load(tmp_path / ("g%d.npy" % rep))
+        assert got.dtype == full.dtype and (got == full[:cut]).all()
+
+
 def test_shard_bounds_cover():
     from vntrseek_b200.dist import shard_bounds
     for n in (0, 1, 7, 1000001):

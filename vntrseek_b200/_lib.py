@@ -67,7 +67,8 @@ class DpDesc(C.Structure):
 
 class ProcluParams(C.Structure):
     _fields_ = [("cutoff", C.c_int32), ("maxerrors", C.c_int32), ("option_r", C.c_int32),
-                ("count_cells", C.c_int32), ("key_budget", C.c_int64)]
+                ("count_cells", C.c_int32), ("key_budget", C.c_int64), ("links_on_device", C.c_int32),
+                ("reserved_", C.c_int32)]
 
 
 class ProcluStats(C.Structure):
@@ -75,7 +76,7 @@ class ProcluStats(C.Structure):
                 ("profile_alignments", C.c_uint64), ("profile_alignments_success", C.c_uint64),
                 ("confirmed", C.c_uint64), ("dp_cells", C.c_int64), ("candidate_keys", C.c_int64),
                 ("chunks", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
-                ("dp_alg_bytes", C.c_int64)]
+                ("dp_alg_bytes", C.c_int64), ("dp_cells_sweep", C.c_int64), ("dp_alg_bytes_sweep", C.c_int64)]
 
 
 class JoinStats(C.Structure):
@@ -125,6 +126,8 @@ def _declare2(L):
     L.vsk_proclu_run_resident.argtypes = [vp, vp, vp, C.POINTER(ProcluParams), C.POINTER(vp)]
     L.vsk_proclu_result_links.argtypes = [vp, C.POINTER(vp)]
     L.vsk_proclu_result_links.restype = C.c_int64
+    L.vsk_proclu_result_links_dev.argtypes = [vp, C.POINTER(vp)]
+    L.vsk_proclu_result_links_dev.restype = C.c_int64
     L.vsk_proclu_result_stats.argtypes = [vp, C.POINTER(ProcluStats)]
     L.vsk_proclu_result_stats.restype = None
     L.vsk_proclu_result_free.argtypes = [vp]
@@ -139,6 +142,7 @@ def _declare2(L):
     L.vsk_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
     L.vsk_profile_enable.argtypes = [vp, C.c_int]
     L.vsk_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    L.vsk_profile_read_sweep.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     L.vsk_profile_stages.argtypes = [vp, C.c_char_p, C.c_size_t]
     L.vsk_int_peak.argtypes = [vp, C.POINTER(C.c_double)]
     L.vsk_pair_dp_static.argtypes = [vp, vp, C.c_int64, vp, C.c_int64, C.POINTER(DpDesc), C.c_int64, vp]

@@ -83,6 +83,7 @@ class Context:
         if table.size != 501501:
             raise VskError("distance table must have 501501 bytes")
         self.h = C.c_void_p()
+        self.device = device
         rc = lib().vsk_init(C.byref(self.h), device, table)
         if rc != 0:
             raise VskError(f"vsk_init failed ({rc}): no usable CUDA device or bad table")
@@ -113,6 +114,12 @@ class Context:
     def profile_read(self):
         ms, n = C.c_double(), C.c_int64()
         self._check(lib().vsk_profile_read(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def profile_read_sweep(self):
+        """(summed ms, launches) of the forward-sweep kernel alone since the last call"""
+        ms, n = C.c_double(), C.c_int64()
+        self._check(lib().vsk_profile_read_sweep(self.h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
     def profile_stages(self):
@@ -286,12 +293,35 @@ class _ResultOwner:
         self.res = None
 
 
-def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=True, count_cells=False):
+class DeviceLinks:
+    """The link table of a run, left in HBM (vsk_proclu_result_links_dev): `n` records of
+    LINK_DTYPE at device address `ptr`.  It belongs to the context and is overwritten by the
+    context's next run.  `.tensor()` views it as a torch int32 tensor [n, 7] without a copy."""
+
+    def __init__(self, ptr, n, device):
+        self.ptr, self.n, self.device = ptr, n, device
+        nf = LINK_DTYPE.itemsize // 4
+        self.__cuda_array_interface__ = {"shape": (n, nf), "typestr": "<i4", "data": (ptr or 0, True), "version": 2}
+
+    def __len__(self):
+        return self.n
+
+    def tensor(self):
+        import torch
+        nf = LINK_DTYPE.itemsize // 4
+        if self.n == 0:
+            return torch.zeros((0, nf), dtype=torch.int32, device="cuda:%d" % self.device)
+        return torch.as_tensor(self, device="cuda:%d" % self.device)
+
+
+def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=True, count_cells=False,
+           links_on_device=False):
     """vsk_proclu_run (reads = TRSetHandle, host buffers) or vsk_proclu_run_resident
     (reads = ResidentReads).  Returns (links structured array, stats dict).  The array is a
     view of the result's page-locked buffer (no copy); the buffer goes back to the
-    context when the array is dropped."""
-    prm = ProcluParams(cutoff, maxerrors, 0, int(count_cells), key_budget)
+    context when the array is dropped.  links_on_device=True: the links are not copied to the
+    host; a DeviceLinks comes back instead (the send buffer of dist.allgather_links)."""
+    prm = ProcluParams(cutoff, maxerrors, 0, int(count_cells), key_budget, int(links_on_device), 0)
     res = C.c_void_p()
     if isinstance(reads, ResidentReads):
         ctx._check(lib().vsk_proclu_run_resident(ctx.h, refs.h, reads.h, C.byref(prm), C.byref(res)))
@@ -300,6 +330,11 @@ def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=T
     st = ProcluStats()
     lib().vsk_proclu_result_stats(res, C.byref(st))
     links = None
+    if links_on_device:
+        ptr = C.c_void_p()
+        n = lib().vsk_proclu_result_links_dev(res, C.byref(ptr))
+        lib().vsk_proclu_result_free(res)
+        return DeviceLinks(ptr.value, int(n), ctx.device), _stats_dict(st)
     if fetch_links:
         ptr = C.c_void_p()
         n = lib().vsk_proclu_result_links(res, C.byref(ptr))

@@ -46,28 +46,23 @@ extern "C" int vsk_load_distance_file(const char *path, uint8_t *out) {
     return rc;
 }
 
-extern "C" int vsk_init(vsk_ctx **out, int device, const uint8_t *sm) {
-    if (!out || !sm) return VSK_ERR_ARG;
-    *out = nullptr;
-    int ndev = 0;
-    cudaError_t e = cudaGetDeviceCount(&ndev);
-    if (e != cudaSuccess || ndev == 0)
-        return vsk_fail(nullptr, VSK_ERR_CUDA, "no CUDA device (%s); libvsk has no CPU path",
-                        cudaGetErrorString(e));
-    if (device < 0 || device >= ndev) return vsk_fail(nullptr, VSK_ERR_ARG, "bad device %d", device);
-    vsk_ctx *ctx = new vsk_ctx();
-    ctx->device = device;
+static int init_device(vsk_ctx *ctx, const uint8_t *sm) {
+    const int device = ctx->device;
     VSK_CUDA(ctx, cudaSetDevice(device));
     cudaDeviceProp prop;
     VSK_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     VSK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    {  // freed stream-ordered memory stays in the pool: the work buffers are re-used launch after launch
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-            uint64_t thr = ~0ull;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
-        }
+    {  // freed stream-ordered memory stays in the context's pool: the work buffers are re-used launch after launch
+        cudaMemPoolProps pp;
+        memset(&pp, 0, sizeof pp);
+        pp.allocType = cudaMemAllocationTypePinned;
+        pp.handleTypes = cudaMemHandleTypeNone;
+        pp.location.type = cudaMemLocationTypeDevice;
+        pp.location.id = device;
+        VSK_CUDA(ctx, cudaMemPoolCreate(&ctx->pool, &pp));
+        uint64_t thr = ~0ull;
+        VSK_CUDA(ctx, cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &thr));
     }
     // symmetric expansion of the triangular table (EVALDISTANCE, profile.h:1100-1103)
     std::vector<uint8_t> full((size_t)VSK_NIDS * VSK_DROW, 0);
@@ -96,6 +91,28 @@ extern "C" int vsk_init(vsk_ctx **out, int device, const uint8_t *sm) {
     VSK_CUDA(ctx, cudaMemcpy(ctx->d_dist, full.data(), full.size(), cudaMemcpyHostToDevice));
     VSK_CUDA(ctx, cudaMemcpy(ctx->d_gapnd, gapnd.data(), gapnd.size() * sizeof(uint16_t),
                              cudaMemcpyHostToDevice));
+    // vsk_pair_dp_static must not load a module or allocate when it is called: its fixed device
+    // array and its kernel become resident here
+    return vsk_dp_static_setup(ctx);
+}
+
+extern "C" int vsk_init(vsk_ctx **out, int device, const uint8_t *sm) {
+    if (!out || !sm) return VSK_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return vsk_fail(nullptr, VSK_ERR_CUDA, "no CUDA device (%s); libvsk has no CPU path",
+                        cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return vsk_fail(nullptr, VSK_ERR_ARG, "bad device %d", device);
+    vsk_ctx *ctx = new vsk_ctx();
+    ctx->device = device;
+    const int rc = init_device(ctx, sm);
+    if (rc != VSK_OK) {  // nobody can ask this context for its error text: print it, release what was made
+        fprintf(stderr, "libvsk: vsk_init: %s\n", ctx->err.c_str());
+        vsk_destroy(ctx);
+        return rc;
+    }
     *out = ctx;
     return VSK_OK;
 }
@@ -109,6 +126,7 @@ extern "C" void vsk_destroy(vsk_ctx *ctx) {
     cudaFree(ctx->d_dp_scratch);
     cudaFree(ctx->d_tiny_dense);
     cudaFree(ctx->d_tiny_ktab);
+    cudaFree(ctx->d_links);
     for (int i = 0; i < 2; ++i)
         if (ctx->dd_stream[i]) cudaStreamDestroy(ctx->dd_stream[i]);
     for (int i = 0; i < 4; ++i)
@@ -116,6 +134,7 @@ extern "C" void vsk_destroy(vsk_ctx *ctx) {
     for (auto &b : ctx->pin_free) cudaFreeHost(b.first);
     for (void *m : ctx->dd_mem) cudaFree(m);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     delete ctx;
 }
 
@@ -476,7 +495,30 @@ extern "C" int vsk_profile_read(vsk_ctx *ctx, double *dp_ms, int64_t *dp_launche
     return VSK_OK;
 }
 
-// Integer-pipe peak on this device: independent chains of IADD3 / VIMNMX / IMAD.
+extern "C" int vsk_profile_read_sweep(vsk_ctx *ctx, double *sweep_ms, int64_t *sweep_launches) {
+    if (!ctx) return VSK_ERR_ARG;
+    VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < 2; ++i)
+        if (ctx->dd_stream[i]) VSK_CUDA(ctx, cudaStreamSynchronize(ctx->dd_stream[i]));
+    double tot = 0;
+    for (size_t i = 0; i + 1 < ctx->prof_sweep_events.size(); i += 2) {
+        float ms = 0;
+        VSK_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->prof_sweep_events[i], ctx->prof_sweep_events[i + 1]));
+        tot += ms;
+        cudaEventDestroy(ctx->prof_sweep_events[i]);
+        cudaEventDestroy(ctx->prof_sweep_events[i + 1]);
+    }
+    if (sweep_ms) *sweep_ms = tot;
+    if (sweep_launches) *sweep_launches = (int64_t)(ctx->prof_sweep_events.size() / 2);
+    ctx->prof_sweep_events.clear();
+    return VSK_OK;
+}
+
+// Integer-pipe peak on this device: independent chains of add / min / multiply-add.  ptxas turns
+// one chain step (a+b; min(a, c+i); a*3+k) into TWO instructions, VIADDMNMX (DPX: add and min in
+// one, ALU pipe) and IMAD (FMA pipe; the +k folds into the next step's immediate), so the figure
+// counts 3 integer operations per 2 issued instructions: above the plain issue limit of one
+// instruction per clock per scheduler (profiles/r02_int_peak_sass.txt).
 __global__ void __launch_bounds__(256) vsk_int_peak_kernel(int *out, int iters, int seed) {
     int a[8];
 #pragma unroll

@@ -26,6 +26,8 @@
 
 #include <cstdlib>
 
+#include <mutex>
+
 #include "vsk_internal.cuh"
 
 #define DP_WARPS 4
@@ -761,7 +763,25 @@ static __device__ __align__(256) unsigned char vsk_dp_static_scratch[sizeof(VskS
 // In host code the name above is only a stand-in for the device array; the address a
 // kernel can use has to be asked for, once per device, with that device current.
 static VskStaticScratch *g_static_dev_addr[64];
-static int g_static_attr_set[64];
+static std::mutex g_static_mutex;
+
+// Per-device set-up of vsk_pair_dp_static, done by vsk_init for the context's device (with that
+// device current): looks up the device address of the fixed array and sets the kernel attribute.
+// Under CUDA's lazy module loading this is also what makes the array and the kernel image
+// resident, so after vsk_init the entry point itself neither loads nor allocates anything.
+// Guarded: two host threads may create contexts (or make their first call) at the same time.
+int vsk_dp_static_setup(vsk_ctx *ctx) {
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= 64) return VSK_OK;  // the entry point refuses such a device itself
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (g_static_dev_addr[dev]) return VSK_OK;
+    void *addr = nullptr;
+    VSK_CUDA(ctx, cudaGetSymbolAddress(&addr, vsk_dp_static_scratch));
+    VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)DP_SMEM_BYTES));
+    g_static_dev_addr[dev] = static_cast<VskStaticScratch *>(addr);
+    return VSK_OK;
+}
 
 extern "C" int vsk_pair_dp_static(vsk_ctx *ctx, const uint16_t *d_left_ids, int64_t n_left_ids,
                                   const uint16_t *d_top_ids, int64_t n_top_ids, const vsk_dp_desc *pairs,
@@ -780,22 +800,21 @@ extern "C" int vsk_pair_dp_static(vsk_ctx *ctx, const uint16_t *d_left_ids, int6
             return vsk_fail(ctx, VSK_ERR_ARG, "vsk_pair_dp_static: pair %lld has %d columns (allowed 1..%d)",
                             (long long)i, p.l2, VSK_MAXPROF);
         if (p.left_off < 0 || p.left_off + p.l1 > n_left_ids || p.top_off < 0 || p.top_off + p.l2 > n_top_ids ||
-            p.out_idx < 0 || p.out_idx >= n || (p.br >= 0 && !(p.svector > 0.0)))
+            p.out_idx < 0 || p.out_idx >= n)
             return vsk_fail(ctx, VSK_ERR_ARG, "vsk_pair_dp_static: pair %lld is out of range", (long long)i);
+        // a band must be the one vsk_band_params gives for these lengths (the kernel's row ranges rely on it)
+        if (p.br >= 0 && (p.svector != (double)p.l2 / (double)p.l1 || p.br < 7 || p.br > 2 * VSK_MAXPROF))
+            return vsk_fail(ctx, VSK_ERR_ARG,
+                            "vsk_pair_dp_static: pair %lld: br/svector are not what vsk_band_params returns for %d x %d",
+                            (long long)i, p.l1, p.l2);
     }
     if (n == 0) return VSK_OK;
     const int dev = ctx->device;
     if (dev < 0 || dev >= 64) return vsk_fail(ctx, VSK_ERR_ARG, "vsk_pair_dp_static: device %d not supported", dev);
     VSK_CUDA(ctx, cudaSetDevice(dev));
-    if (!g_static_dev_addr[dev]) {  // first call on this device: set-up (do it before any stream capture)
-        void *addr = nullptr;
-        VSK_CUDA(ctx, cudaGetSymbolAddress(&addr, vsk_dp_static_scratch));
-        g_static_dev_addr[dev] = static_cast<VskStaticScratch *>(addr);
-    }
-    if (!g_static_attr_set[dev]) {
-        VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)DP_SMEM_BYTES));
-        g_static_attr_set[dev] = 1;
+    if (!g_static_dev_addr[dev]) {  // vsk_init normally did this already
+        const int rc = vsk_dp_static_setup(ctx);
+        if (rc) return rc;
     }
     VskStaticScratch *S = g_static_dev_addr[dev];
     // the array keeps what the previous call left in it: the work counter must start at zero;

@@ -795,10 +795,21 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
         uint32_t *dir = d_dir + (size_t)(b & 1) * half_words;
         int *scr = d_scr + (size_t)(b & 1) * scr_ints;
         if (n_warp > 0 && b <= h_q8_first) {
+            cudaEvent_t pe0 = nullptr, pe1 = nullptr;
+            if (ctx->profile) {
+                VSK_CUDA(ctx, cudaEventCreate(&pe0));
+                VSK_CUDA(ctx, cudaEventCreate(&pe1));
+                VSK_CUDA(ctx, cudaEventRecord(pe0, st));
+            }
             vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, dd_smem, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
                                                                     batch_words, (int)n_warp, ctx->d_dist, ctx->d_gapnd,
                                                                     scr, stride, dir, d_queue, d_out);
             ctx->launches++;
+            if (ctx->profile) {
+                VSK_CUDA(ctx, cudaEventRecord(pe1, st));
+                ctx->prof_sweep_events.push_back(pe0);
+                ctx->prof_sweep_events.push_back(pe1);
+            }
         }
         if (n_q8 > 0 && b >= h_q8_first) {
             vsk_dp_q8dir_kernel<<<grid8, DQ_WARPS * 32, dq_smem, st>>>(

@@ -219,13 +219,13 @@ static int flush_batch(vsk_ctx *ctx, Batch &B, int maxerrors, vsk_flank_stats *s
         if (maxlen > VSK_MAXPROF) return vsk_fail(ctx, VSK_ERR_ARG, "flank longer than %d characters", VSK_MAXPROF);
         std::vector<int32_t> lut((size_t)maxlen + 1);
         for (int k = 0; k <= maxlen; ++k) lut[(size_t)k] = std::min(8, (int)(0.4 * k + .01));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_pool, B.pool.size() + 16, s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_refs, sizeof(vsk_flankrec) * (B.ref_recs.size() + 1), s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_reads, sizeof(vsk_flankrec) * (B.read_recs.size() + 1), s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_pr, sizeof(int32_t) * (size_t)n, s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_pf, sizeof(int32_t) * (size_t)n, s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_lut, sizeof(int32_t) * lut.size(), s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_out, sizeof(uint32_t) * (size_t)n, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pool, B.pool.size() + 16, ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_refs, sizeof(vsk_flankrec) * (B.ref_recs.size() + 1), ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_reads, sizeof(vsk_flankrec) * (B.read_recs.size() + 1), ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pr, sizeof(int32_t) * (size_t)n, ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pf, sizeof(int32_t) * (size_t)n, ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_lut, sizeof(int32_t) * lut.size(), ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_out, sizeof(uint32_t) * (size_t)n, ctx->pool, s));
         VSK_CUDA(ctx, cudaMemcpyAsync(d_pool, B.pool.data(), B.pool.size(), cudaMemcpyHostToDevice, s));
         VSK_CUDA(ctx, cudaMemcpyAsync(d_refs, B.ref_recs.data(), sizeof(vsk_flankrec) * B.ref_recs.size(), cudaMemcpyHostToDevice, s));
         VSK_CUDA(ctx, cudaMemcpyAsync(d_reads, B.read_recs.data(), sizeof(vsk_flankrec) * B.read_recs.size(), cudaMemcpyHostToDevice, s));
@@ -474,13 +474,13 @@ extern "C" int vsk_flank_pairs(vsk_ctx *ctx, const char *pool, int64_t pool_byte
             if (maxlen > VSK_MAXPROF) return vsk_fail(ctx, VSK_ERR_ARG, "flank longer than %d characters", VSK_MAXPROF);
             std::vector<int32_t> lut((size_t)maxlen + 1);
             for (int k = 0; k <= maxlen; ++k) lut[(size_t)k] = std::min(8, (int)(0.4 * k + .01));
-            VSK_CUDA(ctx, cudaMallocAsync(&d_pool, B.pool.size() + 16, s));
-            VSK_CUDA(ctx, cudaMallocAsync(&d_refs, sizeof(vsk_flankrec) * (B.ref_recs.size() + 1), s));
-            VSK_CUDA(ctx, cudaMallocAsync(&d_reads, sizeof(vsk_flankrec) * (B.read_recs.size() + 1), s));
-            VSK_CUDA(ctx, cudaMallocAsync(&d_pr, sizeof(int32_t) * (size_t)n, s));
-            VSK_CUDA(ctx, cudaMallocAsync(&d_pf, sizeof(int32_t) * (size_t)n, s));
-            VSK_CUDA(ctx, cudaMallocAsync(&d_lut, sizeof(int32_t) * lut.size(), s));
-            VSK_CUDA(ctx, cudaMallocAsync(&d_out, sizeof(uint32_t) * (size_t)n, s));
+            VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pool, B.pool.size() + 16, ctx->pool, s));
+            VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_refs, sizeof(vsk_flankrec) * (B.ref_recs.size() + 1), ctx->pool, s));
+            VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_reads, sizeof(vsk_flankrec) * (B.read_recs.size() + 1), ctx->pool, s));
+            VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pr, sizeof(int32_t) * (size_t)n, ctx->pool, s));
+            VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pf, sizeof(int32_t) * (size_t)n, ctx->pool, s));
+            VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_lut, sizeof(int32_t) * lut.size(), ctx->pool, s));
+            VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_out, sizeof(uint32_t) * (size_t)n, ctx->pool, s));
             VSK_CUDA(ctx, cudaMemcpyAsync(d_pool, B.pool.data(), B.pool.size(), cudaMemcpyHostToDevice, s));
             VSK_CUDA(ctx, cudaMemcpyAsync(d_refs, B.ref_recs.data(), sizeof(vsk_flankrec) * B.ref_recs.size(), cudaMemcpyHostToDevice, s));
             VSK_CUDA(ctx, cudaMemcpyAsync(d_reads, B.read_recs.data(), sizeof(vsk_flankrec) * B.read_recs.size(), cudaMemcpyHostToDevice, s));

@@ -25,6 +25,9 @@ struct vsk_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    // stream-ordered allocations come from a pool of this context (freed memory stays in it between
+    // runs); the device's default pool, which a host application may use itself, is left alone
+    cudaMemPool_t pool = nullptr;
     uint8_t *d_dist = nullptr;    // [VSK_NIDS][VSK_DROW] symmetric distances
     uint16_t *d_gapnd = nullptr;  // [1024]: d(0,id) | NONDASHES[id] << 8
     uint8_t h_nd[VSK_NIDS];
@@ -41,6 +44,10 @@ struct vsk_ctx {
     // kept for the life of the context so that no launch waits for an allocation
     void *dd_mem[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     size_t dd_cap[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    // accepted links of the last PROCLU run, kept on the device as well (grow-only; what
+    // vsk_proclu_result_links_dev hands out, e.g. as the send buffer of the multi-GPU all-gather)
+    void *d_links = nullptr;
+    size_t d_links_cap = 0;       // bytes
     std::vector<uint8_t> h_dist;  // host copy of the symmetric table
     // dense-alphabet tables of the thread-per-pair DP kernel, cached per id set
     vsk_idset tiny_key;
@@ -56,6 +63,7 @@ struct vsk_ctx {
     // optional per-launch timing of the DP kernel (bench.py's roofline leg)
     bool profile = false;
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs
+    std::vector<cudaEvent_t> prof_sweep_events;  // start/stop pairs around every vsk_dp_dir_kernel launch
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     // stage marks of the PROCLU pipeline (profile mode): name of the stage that ENDS at the event
     std::vector<std::pair<const char *, cudaEvent_t>> stage_marks;
@@ -127,6 +135,8 @@ int vsk_dp_dir_begin(vsk_ctx *ctx);
 int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids, const vsk_dp_job *d_jobs,
                       int64_t n_warp, int64_t n_q8, int K, int32_t max_l1, int4 *d_out, vsk_dp_job **redo,
                       int **redo_count);
+// per-device set-up of vsk_pair_dp_static (address of its fixed device array, kernel attribute)
+int vsk_dp_static_setup(vsk_ctx *ctx);
 // which composition ids occur in d_ids[0..n)
 int vsk_id_presence(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out);
 

@@ -91,7 +91,7 @@ __constant__ int c_nones[15];
 template <typename T>
 static int upload_vec(vsk_ctx *ctx, std::vector<void *> &allocs, const std::vector<T> &h, T **d,
                       int64_t *bytes = nullptr, size_t pad = 8) {
-    VSK_CUDA(ctx, cudaMallocAsync((void **)d, sizeof(T) * (h.size() + pad), ctx->stream));
+    VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)d, sizeof(T) * (h.size() + pad), ctx->pool, ctx->stream));
     allocs.push_back(*d);
     if (!h.empty())
         VSK_CUDA(ctx, cudaMemcpyAsync(*d, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice, ctx->stream));
@@ -138,17 +138,15 @@ __global__ void __launch_bounds__(256) vsk_pack_consensus_kernel(DevTR t, int64_
 
 static int upload_raw(vsk_ctx *ctx, std::vector<void *> &allocs, const uint8_t *h, size_t n, uint8_t **d,
                       int64_t *bytes) {
-    VSK_CUDA(ctx, cudaMallocAsync((void **)d, n + 64, ctx->stream));
+    VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)d, n + 64, ctx->pool, ctx->stream));
     allocs.push_back(*d);
     if (n) VSK_CUDA(ctx, cudaMemcpyAsync(*d, h, n, cudaMemcpyHostToDevice, ctx->stream));
     if (bytes) *bytes += (int64_t)n;
     return VSK_OK;
 }
 
-static void keep_pool(vsk_ctx *ctx);
 
 static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
-    keep_pool(ctx);
     vsk_reads *r = new vsk_reads();
     r->ctx = ctx;
     r->host = ts;
@@ -181,11 +179,11 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
         for (size_t p = 0; p < np; ++p) blk[p + 1] = blk[p] + (ts->cons_off[p + 1] - ts->cons_off[p] + 63) / 64;
         const int64_t nblk = blk[np];
         if ((rc = upload_vec(ctx, r->allocs, blk, &r->d.cons_blk, &r->h2d_bytes))) { *out = r; return rc; }
-        VSK_CUDA(ctx, cudaMallocAsync((void **)&r->d.cons_planes, sizeof(uint64_t) * 4 * (size_t)(nblk + 1), ctx->stream));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)&r->d.cons_planes, sizeof(uint64_t) * 4 * (size_t)(nblk + 1), ctx->pool, ctx->stream));
         r->allocs.push_back(r->d.cons_planes);
-        VSK_CUDA(ctx, cudaMallocAsync((void **)&r->d.cons_codes, sizeof(uint64_t) * 2 * (size_t)(nblk + 1), ctx->stream));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)&r->d.cons_codes, sizeof(uint64_t) * 2 * (size_t)(nblk + 1), ctx->pool, ctx->stream));
         r->allocs.push_back(r->d.cons_codes);
-        VSK_CUDA(ctx, cudaMallocAsync((void **)&r->d.cons_cnt, sizeof(uint64_t) * (np + 1), ctx->stream));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)&r->d.cons_cnt, sizeof(uint64_t) * (np + 1), ctx->pool, ctx->stream));
         r->allocs.push_back(r->d.cons_cnt);
         if (np) {
             vsk_pack_consensus_kernel<<<(unsigned)((np * 32 + 255) / 256), 256, 0, ctx->stream>>>(r->d, (int64_t)np);
@@ -645,7 +643,7 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
                    vsk_dp_job *__restrict__ jobs, uint32_t *__restrict__ cost, uint8_t *__restrict__ uncertain,
                    unsigned long long *__restrict__ stats /* [0]=cells [1]=n_uncertain [2]=max_l1 [6]=id+result bytes */) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    unsigned long long cells = 0, bytes = 0;
+    unsigned long long cells = 0, bytes = 0, wcells = 0, wbytes = 0;
     unsigned nunc = 0, ntiny = 0;
     int maxl1 = 0;
     if (i < n) {
@@ -696,12 +694,18 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
         nunc = unc;
         maxl1 = j.l1;
         bytes = (unsigned long long)(2 * (j.l1 + j.l2) + 16);  // u16 ids in, one int4 out
+        if (VSK_DP_DIRJOB(j.l2)) {  // the share of the warp-per-pair forward sweep (the dominant kernel)
+            wcells = cells;
+            wbytes = bytes;
+        }
     }
     // one atomic per warp instead of one per thread
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         cells += __shfl_down_sync(0xffffffffu, cells, o);
         bytes += __shfl_down_sync(0xffffffffu, bytes, o);
+        wcells += __shfl_down_sync(0xffffffffu, wcells, o);
+        wbytes += __shfl_down_sync(0xffffffffu, wbytes, o);
         nunc += __shfl_down_sync(0xffffffffu, nunc, o);
         ntiny += __shfl_down_sync(0xffffffffu, ntiny, o);
         maxl1 = max(maxl1, __shfl_down_sync(0xffffffffu, maxl1, o));
@@ -711,6 +715,10 @@ vsk_dp_jobs_kernel(DevTR refs, DevTR reads, const uint64_t *__restrict__ pairs, 
         if (nunc) atomicAdd(&stats[1], (unsigned long long)nunc);
         atomicMax(&stats[2], (unsigned long long)maxl1);
         atomicAdd(&stats[6], bytes);
+        if (wcells) {
+            atomicAdd(&stats[9], wcells);
+            atomicAdd(&stats[10], wbytes);
+        }
         if (ntiny & 0xffffu) atomicAdd(&stats[7], (unsigned long long)(ntiny & 0xffffu));
         if (ntiny >> 16) atomicAdd(&stats[8], (unsigned long long)(ntiny >> 16));
     }
@@ -823,7 +831,7 @@ struct Scratch {  // stream-ordered temporaries of one run
     }
     template <typename T>
     cudaError_t get(T **p, size_t n) {
-        cudaError_t e = cudaMallocAsync((void **)p, sizeof(T) * (n ? n : 1), ctx->stream);
+        cudaError_t e = cudaMallocFromPoolAsync((void **)p, sizeof(T) * (n ? n : 1), ctx->pool, ctx->stream);
         if (e == cudaSuccess) ptrs.push_back(*p);
         return e;
     }
@@ -957,19 +965,6 @@ struct WidenKey {  // chunk-relative sort key -> (read profile << 32) | referenc
         return ((uint64_t)((uint32_t)(k >> shift) + p_begin) << 32) | (k & mask);
     }
 };
-
-static int g_pool_set = 0;
-
-// keep freed stream-ordered memory in the pool between runs
-static void keep_pool(vsk_ctx *ctx) {
-    if (g_pool_set) return;
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) {
-        uint64_t thr = ~0ull;
-        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
-    }
-    g_pool_set = 1;
-}
 
 static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const vsk_proclu_params *prm,
                      int32_t p_begin, int32_t p_end, const int64_t *d_off_emit, int64_t base, int64_t nkeys,
@@ -1137,6 +1132,8 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
         }
     }
     out->stats.dp_alg_bytes += (int64_t)hs[6];
+    out->stats.dp_cells_sweep += (int64_t)hs[9];
+    out->stats.dp_alg_bytes_sweep += (int64_t)hs[10];
     size_t tb4 = 0;
     cub::DeviceRadixSort::SortPairsDescending(nullptr, tb4, cost, cost2, order, order2, ndp, 0, 22, st);
     if (tb4 > tb) { VSK_CUDA(ctx, S.get((uint8_t **)&tmp, tb4)); tb = tb4; }
@@ -1193,6 +1190,26 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
         return vsk_fail(ctx, VSK_ERR_ABORT, "Edit_Distance_multiple_word_NoEndPenaltySeq1 returned -1. Aborting!");
     vsk_stage_mark(ctx, "flank_links");
     const size_t old = out->n_links;
+    // device copy of the link table (the chunks append to it): grow-only buffer of the context
+    if ((old + (size_t)nl) * sizeof(vsk_link_rec) > ctx->d_links_cap) {
+        const size_t want = std::max<size_t>(2 * (old + (size_t)nl) * sizeof(vsk_link_rec), (size_t)1 << 20);
+        void *nb = nullptr;
+        VSK_CUDA(ctx, cudaMalloc(&nb, want));
+        if (old) VSK_CUDA(ctx, cudaMemcpyAsync(nb, ctx->d_links, old * sizeof(vsk_link_rec), cudaMemcpyDeviceToDevice, st));
+        VSK_CUDA(ctx, cudaStreamSynchronize(st));
+        if (ctx->d_links) VSK_CUDA(ctx, cudaFree(ctx->d_links));
+        ctx->d_links = nb;
+        ctx->d_links_cap = want;
+    }
+    if (nl)
+        VSK_CUDA(ctx, cudaMemcpyAsync((vsk_link_rec *)ctx->d_links + old, recs2, sizeof(vsk_link_rec) * (size_t)nl,
+                                      cudaMemcpyDeviceToDevice, st));
+    out->n_links = old + (size_t)nl;
+    if (prm->links_on_device) {  // the caller reads them through vsk_proclu_result_links_dev
+        VSK_CUDA(ctx, cudaStreamSynchronize(st));
+        vsk_stage_mark(ctx, "links_d2h");
+        return VSK_OK;
+    }
     if ((old + (size_t)nl) * sizeof(vsk_link_rec) > out->cap) {
         size_t ncap = 0;
         vsk_link_rec *nb = (vsk_link_rec *)vsk_pin_get(ctx, 2 * (old + (size_t)nl) * sizeof(vsk_link_rec), &ncap);
@@ -1206,7 +1223,6 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
         VSK_CUDA(ctx, cudaMemcpyAsync(out->links + old, recs2, sizeof(vsk_link_rec) * (size_t)nl,
                                       cudaMemcpyDeviceToHost, st));
     VSK_CUDA(ctx, cudaStreamSynchronize(st));
-    out->n_links = old + (size_t)nl;
     out->stats.d2h_bytes += (int64_t)(sizeof(vsk_link_rec) * (size_t)nl);
     vsk_stage_mark(ctx, "links_d2h");
     return VSK_OK;
@@ -1219,7 +1235,6 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
     if (prm->option_r && prm->maxerrors != 0)  // psearch.c:995-999
         return vsk_fail(ctx, VSK_ERR_ARG, "maxerror must be 0 because it will be dynamically generated based on flank length.");
     VSK_CUDA(ctx, cudaSetDevice(ctx->device));
-    keep_pool(ctx);
     const vsk_trset *hq = Q->host;
     const vsk_seedinfo &si = vsk_seeds();
     for (int32_t q = 0; q < hq->n && !Q->checked; ++q) {  // the reference quits on these (psearch.c:784-787, hclust.h:866-869)
@@ -1288,7 +1303,9 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         res->stats.candidates_considered = hraw;
         res->stats.candidate_keys = hoff[(size_t)nprof];
         // chunks of read profiles whose keys fit the budget
-        const int64_t budget = prm->key_budget > 0 ? prm->key_budget : (int64_t)256 << 20;
+        int64_t budget = prm->key_budget > 0 ? prm->key_budget : (int64_t)256 << 20;
+        if (prm->key_budget <= 0)
+            if (const char *e = getenv("VSK_KEY_BUDGET")) budget = std::max<int64_t>(1024, atoll(e));
         int32_t pb = 0;
         while (pb < nprof && rc == VSK_OK) {
             int32_t pe = pb + 2;
@@ -1320,6 +1337,11 @@ extern "C" int vsk_proclu_run(vsk_ctx *ctx, const vsk_refs *R, const vsk_trset *
 extern "C" int64_t vsk_proclu_result_links(const vsk_proclu_result *r, const vsk_link **links) {
     if (!r) return 0;
     if (links) *links = reinterpret_cast<const vsk_link *>(r->links);
+    return (int64_t)r->n_links;
+}
+extern "C" int64_t vsk_proclu_result_links_dev(const vsk_proclu_result *r, const vsk_link **d_links) {
+    if (!r) return 0;
+    if (d_links) *d_links = r->n_links ? reinterpret_cast<const vsk_link *>(r->ctx->d_links) : nullptr;
     return (int64_t)r->n_links;
 }
 extern "C" void vsk_proclu_result_stats(const vsk_proclu_result *r, vsk_proclu_stats *s) {

@@ -237,11 +237,11 @@ static int rf_flush(vsk_ctx *ctx, std::string &pool, std::vector<RfRec> &recs, s
         uint8_t *d_pool = nullptr;
         RfRec *d_recs = nullptr;
         int32_t *d_pa = nullptr, *d_pb = nullptr, *d_out = nullptr;
-        VSK_CUDA(ctx, cudaMallocAsync(&d_pool, pool.size() + 16, s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_recs, sizeof(RfRec) * (recs.size() + 1), s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_pa, sizeof(int32_t) * (size_t)n, s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_pb, sizeof(int32_t) * (size_t)n, s));
-        VSK_CUDA(ctx, cudaMallocAsync(&d_out, sizeof(int32_t) * 4 * (size_t)n, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pool, pool.size() + 16, ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_recs, sizeof(RfRec) * (recs.size() + 1), ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pa, sizeof(int32_t) * (size_t)n, ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pb, sizeof(int32_t) * (size_t)n, ctx->pool, s));
+        VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_out, sizeof(int32_t) * 4 * (size_t)n, ctx->pool, s));
         VSK_CUDA(ctx, cudaMemcpyAsync(d_pool, pool.data(), pool.size(), cudaMemcpyHostToDevice, s));
         VSK_CUDA(ctx, cudaMemcpyAsync(d_recs, recs.data(), sizeof(RfRec) * recs.size(), cudaMemcpyHostToDevice, s));
         VSK_CUDA(ctx, cudaMemcpyAsync(d_pa, pa.data(), sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, s));
@@ -500,11 +500,11 @@ extern "C" int vsk_nbdist_pairs(vsk_ctx *ctx, const char *a, const int64_t *a_of
     RfRec *d_recs = nullptr;
     int32_t *d_pa = nullptr, *d_pb = nullptr, *d_out = nullptr;
     std::vector<int32_t> res((size_t)n * 4);
-    VSK_CUDA(ctx, cudaMallocAsync(&d_pool, pool.size() + 16, s));
-    VSK_CUDA(ctx, cudaMallocAsync(&d_recs, sizeof(RfRec) * recs.size(), s));
-    VSK_CUDA(ctx, cudaMallocAsync(&d_pa, sizeof(int32_t) * (size_t)n, s));
-    VSK_CUDA(ctx, cudaMallocAsync(&d_pb, sizeof(int32_t) * (size_t)n, s));
-    VSK_CUDA(ctx, cudaMallocAsync(&d_out, sizeof(int32_t) * 4 * (size_t)n, s));
+    VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pool, pool.size() + 16, ctx->pool, s));
+    VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_recs, sizeof(RfRec) * recs.size(), ctx->pool, s));
+    VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pa, sizeof(int32_t) * (size_t)n, ctx->pool, s));
+    VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_pb, sizeof(int32_t) * (size_t)n, ctx->pool, s));
+    VSK_CUDA(ctx, cudaMallocFromPoolAsync(&d_out, sizeof(int32_t) * 4 * (size_t)n, ctx->pool, s));
     VSK_CUDA(ctx, cudaMemcpyAsync(d_pool, pool.data(), pool.size(), cudaMemcpyHostToDevice, s));
     VSK_CUDA(ctx, cudaMemcpyAsync(d_recs, recs.data(), sizeof(RfRec) * recs.size(), cudaMemcpyHostToDevice, s));
     VSK_CUDA(ctx, cudaMemcpyAsync(d_pa, pa.data(), sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, s));
