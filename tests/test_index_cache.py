@@ -64,3 +64,24 @@ def test_damaged_file_is_rebuilt(sets, damage):
     assert not v.index_cache_verify(ha, p)
     assert v.index_cache_build(ha, p) is False
     assert v.index_cache_verify(ha, p)
+
+
+@pytest.mark.parametrize("threads", ["1", "2", "7", "32"])
+def test_threaded_build_equals_one_thread_build(tmp_path, monkeypatch, threads):
+    """the index is built on several threads (key ranges sorted independently, the reference's own
+    sort replayed over the multi-hit buckets in the reference's order); vsk_index_cache_verify rebuilds
+    it with the plain one-thread builder and compares every array -- for any thread count, with
+    redundancy groups, long patterns (all 14 seed shapes) and low-complexity consensus strings"""
+    import vntrseek_b200 as v
+    from vntrseek_b200 import synth
+    monkeypatch.setenv("VSK_INDEX_THREADS", threads)
+    refs = synth.fast_refs(6000, seed=int(threads) + 3, rot_frac=0.03)
+    ts = v.TRSetHandle.from_packed(refs, is_read=False)
+    p = str(tmp_path / "t.vskidx")
+    assert v.index_cache_build(ts, p) is False
+    assert v.index_cache_verify(ts, p)
+    monkeypatch.setenv("VSK_INDEX_SERIAL", "1")     # and the switch that selects the one-thread build everywhere
+    q = str(tmp_path / "s.vskidx")
+    assert v.index_cache_build(ts, q) is False
+    assert open(p, "rb").read() == open(q, "rb").read()
+    ts.close()

@@ -11,11 +11,14 @@
 // TRANGE <= 4; the 2-key hash's walker list, doublehash.h:334-392, for the rest)
 // are restated here.  Only the identity of the first hit of every pmin group
 // survives into the device index; the rest of a bucket is a set.
+#include <time.h>
 #include <math.h>
 #include <string.h>
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 
 #include "vsk_host.hpp"
 #include "vsk_internal.cuh"
@@ -216,8 +219,25 @@ static inline uint64_t seed_code(const char *seq, int i, const vsk_seedinfo &si,
     return ((uint64_t)c1 << 32) | c2;
 }
 
-int vsk_build_refindex_host(const vsk_trset &refs, vsk_refindex_host &out, std::string &err) {
+static double now_s() {
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec + ts.tv_nsec * 1e-9;
+}
+
+// The straightforward one-thread build: hits appended bucket by bucket through a hash map, the way
+// the reference does it.  Kept as the cross-check of the threaded build below (vsk_index_cache_verify
+// rebuilds with this one; VSK_INDEX_SERIAL=1 selects it everywhere).
+static int build_refindex_serial(const vsk_trset &refs, vsk_refindex_host &out, std::string &err) {
     const vsk_seedinfo &si = vsk_seeds();
+    const bool timing = getenv("VSK_INDEX_TIMING") != nullptr;
+    double t_phase = now_s();
+    auto phase = [&](const char *name) {
+        if (!timing) return;
+        const double t = now_s();
+        fprintf(stderr, "[vsk index] %-10s %.2f s\n", name, t - t_phase);
+        t_phase = t;
+    };
     struct Bucket {
         int t;
         uint64_t code;
@@ -294,6 +314,7 @@ int vsk_build_refindex_host(const vsk_trset &refs, vsk_refindex_host &out, std::
         }
     }
 
+    phase("seed");
     // scatter hits into bucket-contiguous storage, insertion order kept
     const size_t nb = buckets.size(), nh = hit_item.size();
     int64_t acc = 0;
@@ -306,6 +327,12 @@ int vsk_build_refindex_host(const vsk_trset &refs, vsk_refindex_host &out, std::
     std::vector<int32_t>().swap(hit_bucket);
     std::vector<SortItem>().swap(hit_item);
 
+    phase("scatter");
+    if (timing) {
+        size_t multi = 0, multi_hits = 0;
+        for (size_t b = 0; b < nb; ++b) if (buckets[b].count > 1) { ++multi; multi_hits += (size_t)buckets[b].count; }
+        fprintf(stderr, "[vsk index] hits %zu buckets %zu multi-hit buckets %zu (hits in them %zu)\n", nh, nb, multi, multi_hits);
+    }
     // the order in which the reference sorts its buckets (psearch.c:623-648)
     std::vector<int32_t> order;
     order.reserve(nb);
@@ -337,12 +364,14 @@ int vsk_build_refindex_host(const vsk_trset &refs, vsk_refindex_host &out, std::
             }
         }
     }
+    phase("order");
     EasySort sorter;
     for (int32_t b : order) {
         Bucket &bk = buckets[(size_t)b];
         if (bk.count > 1) sorter.sort(items.data() + bk.start, (int)bk.count);
     }
 
+    phase("sort");
     // flatten: per TRANGE codes ascending; entries = distinct (pmin, prof) + multiplicity + group head
     out = vsk_refindex_host();
     out.tuples = tuples;
@@ -386,6 +415,380 @@ int vsk_build_refindex_host(const vsk_trset &refs, vsk_refindex_host &out, std::
         }
         out.bucket_off[t].push_back((int64_t)out.e_prof.size());
     }
+    phase("flatten");
+    return VSK_OK;
+}
+
+// ---- the same index, built on several threads -------------------------------------------------
+// Nothing in the result depends on how the hits get into their buckets, only on (a) the hits of a
+// bucket in insertion order, (b) the order in which the reference sorts its buckets (it decides
+// where the shared GFSR generator stands when a bucket is partitioned) and (c) the final layout.
+// So: every hit becomes a record (key = TRANGE | seed code, stamp = its insertion number), the
+// records are split into key ranges by sampled splitters (stable scatter), each range is sorted
+// stably by key on its own thread -- a bucket is then a run of equal keys, in insertion order,
+// whose first stamp says when the reference created it -- the (few) buckets with more than one
+// hit are put in the reference's sorting order and partitioned one after the other with the
+// restated generator (the only serial step: 0.6 s for 250 K references), and the flattened arrays
+// are written range by range.
+namespace {
+struct HitRec {
+    uint64_t key;    // trange << 60 | seedcode << 30 | seedcode2 : sorts like (trange, code)
+    uint32_t stamp;  // insertion number of the hit
+    int32_t prof;
+    int16_t pmin;
+};
+
+inline uint64_t rec_code(uint64_t key) {  // back to the (seedcode << 32 | seedcode2) the index stores
+    return (((key >> 30) & 0x3fffffffull) << 32) | (key & 0x3fffffffull);
+}
+
+struct MultiBucket {
+    int64_t start;   // first record
+    int32_t count;
+    uint32_t stamp;  // creation = stamp of its first hit
+    uint64_t key;
+};
+
+// runs fn(i) for i in [0, n) on `nt` threads, work handed out in chunks
+template <typename F>
+void parallel_for(int64_t n, int nt, int64_t chunk, F fn) {
+    if (nt <= 1 || n <= chunk) {
+        for (int64_t i = 0; i < n; ++i) fn(i);
+        return;
+    }
+    std::atomic<int64_t> next(0);
+    std::vector<std::thread> th;
+    auto body = [&] {
+        for (;;) {
+            const int64_t b = next.fetch_add(chunk);
+            if (b >= n) break;
+            const int64_t e = std::min(n, b + chunk);
+            for (int64_t i = b; i < e; ++i) fn(i);
+        }
+    };
+    for (int k = 1; k < nt; ++k) th.emplace_back(body);
+    body();
+    for (auto &t : th) t.join();
+}
+}  // namespace
+
+int vsk_build_refindex_host(const vsk_trset &refs, vsk_refindex_host &out, std::string &err) {
+    if (const char *e = getenv("VSK_INDEX_SERIAL"))
+        if (e[0] == '1') return build_refindex_serial(refs, out, err);
+    const vsk_seedinfo &si = vsk_seeds();
+    const bool timing = getenv("VSK_INDEX_TIMING") != nullptr;
+    int nt = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 64u);
+    if (const char *e = getenv("VSK_INDEX_THREADS")) nt = std::max(1, std::min(256, atoi(e)));
+    double t_phase = now_s();
+    auto phase = [&](const char *name) {
+        if (!timing) return;
+        const double t = now_s();
+        fprintf(stderr, "[vsk index] %-10s %.2f s\n", name, t - t_phase);
+        t_phase = t;
+    };
+
+    // ---- which (profile, TRANGE) seedings happen, in the reference's order, and where their hits start
+    struct Seeding { int32_t prof; int16_t t, pmin; int64_t base; };
+    std::vector<Seeding> seedings;
+    int64_t nh = 0;
+    auto add_seeding = [&](int32_t prof, int t, int pmin) {
+        const int len = (int)(refs.cons_off[prof + 1] - refs.cons_off[prof]);
+        seedings.push_back(Seeding{prof, (int16_t)t, (int16_t)pmin, nh});
+        nh += std::max(0, len - si.tsize[t] + 1);
+    };
+    for (int32_t r = 0; r < refs.n; ++r) {
+        const int pmin = refs.patlen[r];
+        if (pmin < 7 || pmin > 5000) {  // psearch.c:518-521
+            err = "pmin(" + std::to_string(pmin) + ") must be in 7-5000 range!";
+            return VSK_ERR_ABORT;
+        }
+        if (!refs.master[r]) continue;  // psearch.c:452-471: non-masters leave the scan list
+        const int t = si.trange_of[pmin];
+        if (t <= 0) continue;
+        for (int o = 0; o < 2; ++o) {
+            const int len = (int)(refs.cons_off[2 * r + o + 1] - refs.cons_off[2 * r + o]);
+            if (si.tsize[t] > len) {  // seqdupPlusTuple, hclust.h:866-869
+                err = "Tuple size (" + std::to_string(si.tsize[t]) + ") is larger than sequence(" +
+                      std::to_string(len) + "). Aborting!";
+                return VSK_ERR_ABORT;
+            }
+        }
+        add_seeding(2 * r, t, pmin);
+        add_seeding(2 * r + 1, t, pmin);
+        const int e = si.err_of[pmin];
+        const int lower = pmin - e;
+        if (lower >= 7 && si.trange_of[lower] <= t - 1) {  // psearch.c:552-577
+            for (int o = 0; o < 2; ++o)
+                if (si.tsize[t - 1] > (int)(refs.cons_off[2 * r + o + 1] - refs.cons_off[2 * r + o])) {
+                    err = "Tuple size is larger than sequence. Aborting!";
+                    return VSK_ERR_ABORT;
+                }
+            add_seeding(2 * r, t - 1, pmin);
+            add_seeding(2 * r + 1, t - 1, pmin);
+        }
+        const int higher = pmin + e;
+        if (higher <= 5000 && si.trange_of[higher] >= t + 1) {  // psearch.c:583-607
+            for (int o = 0; o < 2; ++o)
+                if (si.tsize[t + 1] > (int)(refs.cons_off[2 * r + o + 1] - refs.cons_off[2 * r + o])) {
+                    err = "Tuple size is larger than sequence. Aborting!";
+                    return VSK_ERR_ABORT;
+                }
+            add_seeding(2 * r, t + 1, pmin);
+            add_seeding(2 * r + 1, t + 1, pmin);
+        }
+    }
+    if (nh >= ((int64_t)1 << 32)) {
+        err = "more than 2^32 seed hits in the reference set";
+        return VSK_ERR_ARG;
+    }
+    out = vsk_refindex_host();
+    out.tuples = (uint64_t)nh;
+    out.total_hits = nh;
+    if (nh == 0) return VSK_OK;
+
+    // ---- hit records, in insertion order
+    std::vector<HitRec> rec((size_t)nh);
+    parallel_for((int64_t)seedings.size(), nt, 256, [&](int64_t s) {
+        const Seeding &sd = seedings[(size_t)s];
+        const char *seq = refs.cons.data() + refs.cons_off[sd.prof];
+        const int len = (int)(refs.cons_off[sd.prof + 1] - refs.cons_off[sd.prof]);
+        const int ts = si.tsize[sd.t];
+        int64_t h = sd.base;
+        for (int i = ts - 1; i < len; ++i, ++h) {
+            const uint64_t code = seed_code(seq, i, si, sd.t);
+            HitRec &x = rec[(size_t)h];
+            x.key = ((uint64_t)sd.t << 60) | ((code >> 32) << 30) | (code & 0x3fffffffull);
+            x.stamp = (uint32_t)h;
+            x.prof = sd.prof;
+            x.pmin = sd.pmin;
+        }
+    });
+    std::vector<Seeding>().swap(seedings);
+    phase("seed");
+
+    // ---- key ranges from sampled splitters; stable scatter into them
+    const int want_parts = (int)std::max<int64_t>(1, std::min<int64_t>(4096, nh / 8192));
+    std::vector<uint64_t> split;  // range p holds keys in (split[p-1], split[p]]; the last is open
+    {
+        const int64_t ns = std::min<int64_t>(nh, (int64_t)want_parts * 64);
+        std::vector<uint64_t> sample((size_t)ns);
+        for (int64_t k = 0; k < ns; ++k) sample[(size_t)k] = rec[(size_t)(k * nh / ns)].key;
+        std::sort(sample.begin(), sample.end());
+        for (int p = 1; p < want_parts; ++p) {
+            const uint64_t v = sample[(size_t)((int64_t)p * ns / want_parts)];
+            if (split.empty() || v > split.back()) split.push_back(v);
+        }
+    }
+    const int P = (int)split.size() + 1;
+    auto part_of = [&](uint64_t key) { return (int)(std::lower_bound(split.begin(), split.end(), key) - split.begin()); };
+    const int ns_slices = nt;  // one slice of the insertion order per thread
+    std::vector<int64_t> hist((size_t)ns_slices * P, 0);
+    std::vector<uint16_t> pid((size_t)nh);
+    parallel_for(ns_slices, nt, 1, [&](int64_t sl) {
+        const int64_t b = nh * sl / ns_slices, e = nh * (sl + 1) / ns_slices;
+        int64_t *hrow = hist.data() + (size_t)sl * P;
+        for (int64_t h = b; h < e; ++h) {
+            const int p = part_of(rec[(size_t)h].key);
+            pid[(size_t)h] = (uint16_t)p;
+            ++hrow[p];
+        }
+    });
+    std::vector<int64_t> part_off((size_t)P + 1, 0);
+    {
+        int64_t acc = 0;
+        for (int p = 0; p < P; ++p) {
+            part_off[(size_t)p] = acc;
+            for (int sl = 0; sl < ns_slices; ++sl) {
+                const int64_t c = hist[(size_t)sl * P + p];
+                hist[(size_t)sl * P + p] = acc;  // where slice sl writes its first record of range p
+                acc += c;
+            }
+        }
+        part_off[(size_t)P] = acc;
+    }
+    std::vector<HitRec> srt((size_t)nh);
+    parallel_for(ns_slices, nt, 1, [&](int64_t sl) {
+        const int64_t b = nh * sl / ns_slices, e = nh * (sl + 1) / ns_slices;
+        int64_t *hrow = hist.data() + (size_t)sl * P;
+        for (int64_t h = b; h < e; ++h) srt[(size_t)hrow[pid[(size_t)h]]++] = rec[(size_t)h];
+    });
+    std::vector<HitRec>().swap(rec);
+    std::vector<uint16_t>().swap(pid);
+    phase("scatter");
+
+    // ---- every range sorted stably by key; first use of the 2-key hash's racks; buckets with several hits
+    const uint32_t hsize = 1162687;  // EasyLifeGetPrime(1000000), easylife.c:1620-1645
+    std::vector<std::atomic<uint32_t>> rack_first((size_t)15 * hsize);
+    parallel_for((int64_t)rack_first.size(), nt, 1 << 16, [&](int64_t i) { rack_first[(size_t)i].store(0xffffffffu, std::memory_order_relaxed); });
+    auto rack_of = [&](uint64_t key) {
+        const uint64_t code = rec_code(key);
+        return (uint32_t)((uint32_t)(rjhash((uint32_t)(code >> 32)) + rjhash((uint32_t)code)) % hsize);
+    };
+    std::vector<std::vector<MultiBucket>> multi((size_t)P);
+    std::vector<int64_t> part_entries((size_t)P, 0);     // entries the range will emit (after the replay)
+    std::vector<int64_t> part_codes((size_t)P * 15, 0);  // buckets of the range per TRANGE
+    parallel_for(P, nt, 1, [&](int64_t p) {
+        HitRec *a = srt.data() + part_off[(size_t)p], *z = srt.data() + part_off[(size_t)p + 1];
+        std::stable_sort(a, z, [](const HitRec &x, const HitRec &y) { return x.key < y.key; });
+        for (HitRec *g = a; g < z;) {
+            HitRec *h = g + 1;
+            while (h < z && h->key == g->key) ++h;
+            const int t = (int)(g->key >> 60);
+            ++part_codes[(size_t)p * 15 + t];
+            if (t > 4) {  // doublehash.h:334-392: racks are walked in reverse order of first use
+                std::atomic<uint32_t> &rf = rack_first[(size_t)t * hsize + rack_of(g->key)];
+                uint32_t cur = rf.load(std::memory_order_relaxed);
+                while (g->stamp < cur && !rf.compare_exchange_weak(cur, g->stamp, std::memory_order_relaxed)) {}
+            }
+            if (h - g > 1)
+                multi[(size_t)p].push_back(MultiBucket{(int64_t)(g - srt.data()), (int32_t)(h - g), g->stamp, g->key});
+            g = h;
+        }
+    });
+    phase("sort");
+
+    // ---- the reference's order over the buckets it actually has to partition (psearch.c:623-648)
+    std::vector<MultiBucket> order;
+    {
+        size_t tot = 0;
+        for (auto &v : multi) tot += v.size();
+        order.reserve(tot);
+        for (auto &v : multi) {  // ranges are in key order: ascending (TRANGE, code)
+            order.insert(order.end(), v.begin(), v.end());
+            std::vector<MultiBucket>().swap(v);
+        }
+        // TRANGE <= 4: direct arrays, ascending code -- as they stand.  TRANGE > 4: racks in reverse order
+        // of first use, inside a rack the chain in reverse creation order.
+        auto first_big = std::partition_point(order.begin(), order.end(), [](const MultiBucket &b) { return (b.key >> 60) <= 4; });
+        const int64_t nbig = (int64_t)(order.end() - first_big);
+        MultiBucket *big = order.data() + (first_big - order.begin());
+        std::vector<uint32_t> rfu((size_t)nbig);  // first use of the bucket's rack
+        parallel_for(nbig, nt, 4096, [&](int64_t i) {
+            const int t = (int)(big[i].key >> 60);
+            rfu[(size_t)i] = rack_first[(size_t)t * hsize + rack_of(big[i].key)].load(std::memory_order_relaxed);
+        });
+        std::vector<int64_t> perm((size_t)nbig);
+        for (int64_t i = 0; i < nbig; ++i) perm[(size_t)i] = i;
+        // ascending TRANGE, then descending rack first use, then descending creation
+        std::sort(perm.begin(), perm.end(), [&](int64_t x, int64_t y) {
+            const int tx = (int)(big[x].key >> 60), ty = (int)(big[y].key >> 60);
+            if (tx != ty) return tx < ty;
+            if (rfu[(size_t)x] != rfu[(size_t)y]) return rfu[(size_t)x] > rfu[(size_t)y];
+            return big[x].stamp > big[y].stamp;
+        });
+        std::vector<MultiBucket> sorted((size_t)nbig);
+        for (int64_t i = 0; i < nbig; ++i) sorted[(size_t)i] = big[perm[(size_t)i]];
+        std::copy(sorted.begin(), sorted.end(), big);
+    }
+    std::vector<std::atomic<uint32_t>>().swap(rack_first);
+    phase("order");
+
+    // ---- the reference's sort, bucket after bucket, with the one generator
+    {
+        EasySort sorter;
+        std::vector<SortItem> tmp;
+        for (const MultiBucket &b : order) {
+            tmp.resize((size_t)b.count);
+            HitRec *a = srt.data() + b.start;
+            for (int32_t k = 0; k < b.count; ++k) tmp[(size_t)k] = SortItem{a[k].pmin, a[k].prof};
+            sorter.sort(tmp.data(), b.count);
+            for (int32_t k = 0; k < b.count; ++k) { a[k].pmin = tmp[(size_t)k].pmin; a[k].prof = tmp[(size_t)k].prof; }
+        }
+    }
+    std::vector<MultiBucket>().swap(order);
+    phase("replay");
+
+    // ---- flatten: per TRANGE codes ascending; entries = distinct (pmin, prof) + multiplicity + group head
+    // pass A: how many entries every range emits
+    parallel_for(P, nt, 1, [&](int64_t p) {
+        const HitRec *a = srt.data() + part_off[(size_t)p], *z = srt.data() + part_off[(size_t)p + 1];
+        int64_t ne = 0;
+        std::vector<int32_t> profs;
+        for (const HitRec *g = a; g < z;) {
+            const HitRec *h = g + 1;
+            while (h < z && h->key == g->key) ++h;
+            if (h - g == 1) ++ne;
+            else
+                for (const HitRec *u = g; u < h;) {  // groups of equal pmin; distinct profiles inside
+                    const HitRec *w = u;
+                    profs.clear();
+                    while (w < h && w->pmin == u->pmin) profs.push_back((w++)->prof);
+                    std::sort(profs.begin(), profs.end());
+                    ne += (int64_t)(std::unique(profs.begin(), profs.end()) - profs.begin());
+                    u = w;
+                }
+            g = h;
+        }
+        part_entries[(size_t)p] = ne;
+    });
+    std::vector<int64_t> ent_off((size_t)P + 1, 0), code_off((size_t)(P + 1) * 15, 0);
+    for (int p = 0; p < P; ++p) {
+        ent_off[(size_t)p + 1] = ent_off[(size_t)p] + part_entries[(size_t)p];
+        for (int t = 0; t < 15; ++t)
+            code_off[(size_t)(p + 1) * 15 + t] = code_off[(size_t)p * 15 + t] + part_codes[(size_t)p * 15 + t];
+    }
+    const int64_t ne_total = ent_off[(size_t)P];
+    out.e_pmin.resize((size_t)ne_total);
+    out.e_prof.resize((size_t)ne_total);
+    out.e_mult.resize((size_t)ne_total);
+    out.e_first.resize((size_t)ne_total);
+    out.e_cum.resize((size_t)ne_total);
+    for (int t = 1; t <= 14; ++t) {
+        const int64_t nc = code_off[(size_t)P * 15 + t];
+        out.codes[t].resize((size_t)nc);
+        out.bucket_off[t].resize((size_t)nc + 1);
+    }
+    // pass B: fill.  A TRANGE's buckets are consecutive in key order, so its bucket_off ends where the next
+    // TRANGE's entries begin; that last element is written after the loop.
+    parallel_for(P, nt, 1, [&](int64_t p) {
+        const HitRec *a = srt.data() + part_off[(size_t)p], *z = srt.data() + part_off[(size_t)p + 1];
+        int64_t e = ent_off[(size_t)p];
+        int64_t ci[15];
+        for (int t = 0; t < 15; ++t) ci[t] = code_off[(size_t)p * 15 + t];
+        std::vector<int32_t> profs;
+        for (const HitRec *g = a; g < z;) {
+            const HitRec *h = g + 1;
+            while (h < z && h->key == g->key) ++h;
+            const int t = (int)(g->key >> 60);
+            out.codes[t][(size_t)ci[t]] = rec_code(g->key);
+            out.bucket_off[t][(size_t)ci[t]] = e;
+            ++ci[t];
+            int64_t cum = 0;
+            for (const HitRec *u = g; u < h;) {
+                const HitRec *w = u;
+                profs.clear();
+                while (w < h && w->pmin == u->pmin) profs.push_back((w++)->prof);
+                std::sort(profs.begin(), profs.end());
+                for (size_t k = 0; k < profs.size();) {
+                    size_t m = k;
+                    while (m < profs.size() && profs[m] == profs[k]) ++m;
+                    out.e_pmin[(size_t)e] = u->pmin;
+                    out.e_prof[(size_t)e] = profs[k];
+                    out.e_mult[(size_t)e] = (int32_t)(m - k);
+                    out.e_first[(size_t)e] = u->prof;  // the group's first hit in the reference's bucket order
+                    out.e_cum[(size_t)e] = cum;
+                    cum += (int64_t)(m - k);
+                    ++e;
+                    k = m;
+                }
+                u = w;
+            }
+            g = h;
+        }
+    });
+    {
+        int64_t acc = 0;  // entries before TRANGE t = entries of all smaller TRANGEs
+        for (int t = 1; t <= 14; ++t) {
+            // number of entries of TRANGE t: from the first bucket of the next used TRANGE, or the total
+            int64_t end = ne_total;
+            for (int u = t + 1; u <= 14; ++u)
+                if (!out.codes[u].empty()) { end = out.bucket_off[u][0]; break; }
+            if (!out.codes[t].empty()) out.bucket_off[t][out.codes[t].size()] = end;
+            else out.bucket_off[t][0] = acc;
+            if (!out.codes[t].empty()) acc = end;
+        }
+    }
+    phase("flatten");
     return VSK_OK;
 }
 
@@ -515,7 +918,7 @@ extern "C" int vsk_index_cache_verify(const vsk_trset *refs, const char *path) {
     vsk_refindex_host a, b;
     std::string err;
     if (vsk_refindex_load(a, vsk_refs_fingerprint(*refs), path) != VSK_OK) return VSK_ERR_ARG;
-    const int rc = vsk_build_refindex_host(*refs, b, err);
+    const int rc = build_refindex_serial(*refs, b, err);  // the independent one-thread build
     if (rc) return rc;
     bool same = a.total_hits == b.total_hits && a.tuples == b.tuples && a.e_pmin == b.e_pmin && a.e_prof == b.e_prof &&
                 a.e_mult == b.e_mult && a.e_first == b.e_first && a.e_cum == b.e_cum;

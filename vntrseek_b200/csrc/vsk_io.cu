@@ -272,7 +272,9 @@ extern "C" int vsk_trset_load_leb36(const char *path, int is_read, int maxflank,
         }
         for (auto *q : part) delete q;
         if (!done)
-            for (int k = 1; k < nthreads; ++k) *cut[(size_t)k] = saved[(size_t)k];  // back to the text as read
+            // back to the text as read; descending, so that two cuts on the same newline (a line longer
+            // than a range) put back the character the first of them saved, not the NUL the second saw
+            for (int k = nthreads - 1; k >= 1; --k) *cut[(size_t)k] = saved[(size_t)k];
     }
     if (!done) {
         bool st, rg;

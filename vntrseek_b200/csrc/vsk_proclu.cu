@@ -146,7 +146,29 @@ static int upload_raw(vsk_ctx *ctx, std::vector<void *> &allocs, const uint8_t *
 }
 
 
+// The kernels hold per-string state sized for VSK_MAXPROF columns / characters (look-up tables,
+// carry arrays, the packed path-weight field): longer records are refused here, loudly, instead of
+// being computed wrongly.  (The reference's own limit is MAXPROFILESIZE 5000 path steps, profile.h:1090.)
+int vsk_trset_check_limits(vsk_ctx *ctx, const vsk_trset *ts) {
+    for (int32_t i = 0; i < ts->n; ++i)
+        for (int o = 0; o < 2; ++o) {
+            const size_t p = (size_t)(2 * i + o);
+            const int64_t plen = ts->prof_off[p + 1] - ts->prof_off[p];
+            const int64_t clen = ts->cons_off[p + 1] - ts->cons_off[p];
+            if (plen > VSK_MAXPROF || clen > VSK_MAXPROF)
+                return vsk_fail(ctx, VSK_ERR_ARG, "profile %d has %lld columns (limit %d)", ts->key[(size_t)i],
+                                (long long)std::max(plen, clen), VSK_MAXPROF);
+            const int64_t ll = ts->fl_off[2 * p + 1] - ts->fl_off[2 * p], rl = ts->fl_off[2 * p + 2] - ts->fl_off[2 * p + 1];
+            if (ll > VSK_MAXPROF || rl > VSK_MAXPROF || ts->leftlen[p] > VSK_MAXPROF || ts->rightlen[p] > VSK_MAXPROF)
+                return vsk_fail(ctx, VSK_ERR_ARG, "profile %d has a flank of %lld characters (limit %d)",
+                                ts->key[(size_t)i], (long long)std::max(ll, rl), VSK_MAXPROF);
+        }
+    return VSK_OK;
+}
+
 static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
+    *out = nullptr;
+    if (int lim = vsk_trset_check_limits(ctx, ts)) return lim;
     vsk_reads *r = new vsk_reads();
     r->ctx = ctx;
     r->host = ts;
