@@ -51,10 +51,11 @@ int vsk_timer_stop(vsk_ctx *ctx, float *ms);
 int vsk_profile_enable(vsk_ctx *ctx, int on);
 int vsk_profile_read(vsk_ctx *ctx, double *dp_kernel_ms, int64_t *dp_kernel_launches);
 int vsk_int_peak(vsk_ctx *ctx, double *gops);
-/* profile mode: summed duration and number of launches of the forward-sweep kernel alone
- * (vsk_dp_dir_kernel), events on the side stream each launch runs on.  Launches of consecutive
- * batches overlap at their tails, so the sum can exceed the wall time of the DP stage.        */
-int vsk_profile_read_sweep(vsk_ctx *ctx, double *sweep_ms, int64_t *sweep_launches);
+/* profile mode: the forward-sweep kernel alone (vsk_dp_dir_kernel), events on the side stream each
+ * launch runs on: summed duration and number of its launches, and `busy_ms` = the time during
+ * which at least one launch was running (consecutive batches run on two streams and overlap, so
+ * the sum of the durations exceeds it).                                                        */
+int vsk_profile_read_sweep(vsk_ctx *ctx, double *sweep_ms, int64_t *sweep_launches, double *busy_ms);
 /* profile mode: "stage=ms;..." of the PROCLU pipeline stages since the last call */
 int vsk_profile_stages(vsk_ctx *ctx, char *buf, size_t n);
 
@@ -216,6 +217,12 @@ typedef struct {
     int64_t key_budget;  /* candidate keys per chunk, 0 = default (or $VSK_KEY_BUDGET)  */
     int32_t links_on_device; /* 1: the links stay in HBM only (vsk_proclu_result_links_dev), no D2H */
     int32_t reserved_;
+    /* optional: called after every chunk of reads with the scan-list position reached (read TRs that
+     * are their redundancy group's master, the reads the reference's loop visits, psearch.c:777-845),
+     * the size of that list, and stProfileAlignments so far -- what psearch's per-percent progress
+     * lines report (psearch.c:836-844)                                                             */
+    void (*progress)(void *user, int64_t reads_done, int64_t reads_total, uint64_t profile_alignments);
+    void *progress_user;
 } vsk_proclu_params;
 
 typedef struct {                          /* BLASTSTATS, hclust.h:43-51 */

@@ -68,7 +68,7 @@ class DpDesc(C.Structure):
 class ProcluParams(C.Structure):
     _fields_ = [("cutoff", C.c_int32), ("maxerrors", C.c_int32), ("option_r", C.c_int32),
                 ("count_cells", C.c_int32), ("key_budget", C.c_int64), ("links_on_device", C.c_int32),
-                ("reserved_", C.c_int32)]
+                ("reserved_", C.c_int32), ("progress", C.c_void_p), ("progress_user", C.c_void_p)]
 
 
 class ProcluStats(C.Structure):
@@ -142,7 +142,7 @@ def _declare2(L):
     L.vsk_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
     L.vsk_profile_enable.argtypes = [vp, C.c_int]
     L.vsk_profile_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
-    L.vsk_profile_read_sweep.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    L.vsk_profile_read_sweep.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_double)]
     L.vsk_profile_stages.argtypes = [vp, C.c_char_p, C.c_size_t]
     L.vsk_int_peak.argtypes = [vp, C.POINTER(C.c_double)]
     L.vsk_pair_dp_static.argtypes = [vp, vp, C.c_int64, vp, C.c_int64, C.POINTER(DpDesc), C.c_int64, vp]

@@ -117,10 +117,11 @@ class Context:
         return ms.value, n.value
 
     def profile_read_sweep(self):
-        """(summed ms, launches) of the forward-sweep kernel alone since the last call"""
-        ms, n = C.c_double(), C.c_int64()
-        self._check(lib().vsk_profile_read_sweep(self.h, C.byref(ms), C.byref(n)))
-        return ms.value, n.value
+        """(summed ms, launches, busy ms) of the forward-sweep kernel alone since the last call; busy =
+        time during which at least one of its launches was running (they overlap across two streams)"""
+        ms, n, busy = C.c_double(), C.c_int64(), C.c_double()
+        self._check(lib().vsk_profile_read_sweep(self.h, C.byref(ms), C.byref(n), C.byref(busy)))
+        return ms.value, n.value, busy.value
 
     def profile_stages(self):
         buf = C.create_string_buffer(4096)
@@ -321,7 +322,7 @@ def proclu(ctx, refs, reads, cutoff=88, maxerrors=0, key_budget=0, fetch_links=T
     view of the result's page-locked buffer (no copy); the buffer goes back to the
     context when the array is dropped.  links_on_device=True: the links are not copied to the
     host; a DeviceLinks comes back instead (the send buffer of dist.allgather_links)."""
-    prm = ProcluParams(cutoff, maxerrors, 0, int(count_cells), key_budget, int(links_on_device), 0)
+    prm = ProcluParams(cutoff, maxerrors, 0, int(count_cells), key_budget, int(links_on_device), 0, None, None)
     res = C.c_void_p()
     if isinstance(reads, ResidentReads):
         ctx._check(lib().vsk_proclu_run_resident(ctx.h, refs.h, reads.h, C.byref(prm), C.byref(res)))

@@ -22,6 +22,25 @@ static void die(const char *msg) {
     exit(1);
 }
 
+/* The reference's per-percent progress lines (psearch.c:836-844): "\nP% (ProfileAlignments: N, total
+ * time: T secs)", one for every percent of the scan list, P counting up from 0.  The scan runs chunk by
+ * chunk on the GPU, so the lines of all the marks a chunk crosses appear together when it ends, each with
+ * the ProfileAlignments count reached at that point. */
+static time_t progress_start;
+static int progress_percent = 0;
+static void progress_lines(void *user, int64_t done, int64_t total, uint64_t profile_alignments) {
+    (void) user;
+    if (total <= 0) return;
+    /* the reference prints at most one line per read: marks are P = 0 .. min(100, reads) */
+    while (progress_percent <= 100 && progress_percent < 101 &&
+           (int) (100 * (2 * done) / (double) (2 * total)) >= progress_percent && progress_percent <= done) {
+        fprintf(stderr, "\n%d%% (ProfileAlignments: %llu, total time: %.1lf secs)", progress_percent,
+                (unsigned long long) profile_alignments, (double) (time(NULL) - progress_start));
+        progress_percent++;
+    }
+    fflush(stderr);
+}
+
 int main(int argc, char **argv) {
     char outputfile[1100], mapfile[1100], edgesfile[1100], buffer[1100];
     const char *edgesIn = NULL;
@@ -83,6 +102,7 @@ int main(int argc, char **argv) {
         exit(1);
     }
     startTime = time(NULL);
+    progress_start = startTime;
     {
         FILE *f = fopen(argv[1], "r");
         if (!f) { fprintf(stderr, "\nERROR: Unable to open input file '%s'", argv[1]); exit(1); }
@@ -162,6 +182,7 @@ int main(int argc, char **argv) {
         fprintf(stderr, "(total time: %.1lf secs)", (double) (time(NULL) - startTime));
         fprintf(stderr, "\nScanning reads...");
         memset(&prm, 0, sizeof prm);
+        prm.progress = progress_lines;
         prm.cutoff = cutoff2;
         prm.maxerrors = maxerrors;
         prm.option_r = option_r;

@@ -495,21 +495,39 @@ extern "C" int vsk_profile_read(vsk_ctx *ctx, double *dp_ms, int64_t *dp_launche
     return VSK_OK;
 }
 
-extern "C" int vsk_profile_read_sweep(vsk_ctx *ctx, double *sweep_ms, int64_t *sweep_launches) {
+extern "C" int vsk_profile_read_sweep(vsk_ctx *ctx, double *sweep_ms, int64_t *sweep_launches, double *busy_ms) {
     if (!ctx) return VSK_ERR_ARG;
     VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     for (int i = 0; i < 2; ++i)
         if (ctx->dd_stream[i]) VSK_CUDA(ctx, cudaStreamSynchronize(ctx->dd_stream[i]));
     double tot = 0;
-    for (size_t i = 0; i + 1 < ctx->prof_sweep_events.size(); i += 2) {
-        float ms = 0;
-        VSK_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->prof_sweep_events[i], ctx->prof_sweep_events[i + 1]));
+    const size_t n = ctx->prof_sweep_events.size() / 2;
+    std::vector<std::pair<double, double>> iv;  // [start, end) of every launch, ms since the first start event
+    for (size_t i = 0; i < n; ++i) {
+        float ms = 0, t0 = 0;
+        VSK_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->prof_sweep_events[2 * i], ctx->prof_sweep_events[2 * i + 1]));
+        VSK_CUDA(ctx, cudaEventElapsedTime(&t0, ctx->prof_sweep_events[0], ctx->prof_sweep_events[2 * i]));
         tot += ms;
-        cudaEventDestroy(ctx->prof_sweep_events[i]);
-        cudaEventDestroy(ctx->prof_sweep_events[i + 1]);
+        iv.emplace_back((double)t0, (double)t0 + ms);
     }
+    for (cudaEvent_t e : ctx->prof_sweep_events) cudaEventDestroy(e);
+    // launches of consecutive batches run on two streams and overlap: the time during which at least one
+    // of them was running is the length of the union of their intervals
+    std::sort(iv.begin(), iv.end());
+    double busy = 0, cur_a = 0, cur_b = -1;
+    for (auto &x : iv) {
+        if (cur_b < cur_a || x.first > cur_b) {
+            if (cur_b >= cur_a) busy += cur_b - cur_a;
+            cur_a = x.first;
+            cur_b = x.second;
+        } else if (x.second > cur_b) {
+            cur_b = x.second;
+        }
+    }
+    if (cur_b >= cur_a) busy += cur_b - cur_a;
     if (sweep_ms) *sweep_ms = tot;
-    if (sweep_launches) *sweep_launches = (int64_t)(ctx->prof_sweep_events.size() / 2);
+    if (sweep_launches) *sweep_launches = (int64_t)n;
+    if (busy_ms) *busy_ms = busy;
     ctx->prof_sweep_events.clear();
     return VSK_OK;
 }

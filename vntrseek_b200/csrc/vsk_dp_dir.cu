@@ -27,15 +27,20 @@
 #include "vsk_internal.cuh"
 
 #define DD_WARPS 4
-#define DD_TBYTES 8192
+#define DD_TBYTES 24576  // per warp: query profile of a strip [row symbol][lane][CPL], or the compact table [na][nb]
 #define DD_MAXCPL 16
-#define DD_STEP_OV 3  // cost of a wavefront step that does not depend on the cells per lane, in cells
+#define DD_MAXNA 96      // row alphabets up to this size can have a query profile (at 8 columns per lane)
 #define DD_FULL 0xffffffffu
+// how the sweep finds d(row symbol, column symbol)
+#define DD_GLOBAL 0  // one byte load per cell from the symmetric table in global memory
+#define DD_SMEMT 1   // one byte load per cell from the pair's compact table in shared memory
+#define DD_QP 2      // one vector load per row from the strip's query profile, bytes picked by dp4a
 
 struct DdWarpSmem {
-    uint8_t T[DD_TBYTES];   // compact substitution table [na][nb]
+    uint8_t T[DD_TBYTES];   // query profile of the current strip, or compact substitution table [na][nb]
     uint32_t bmL[32], bmT[32];
     uint16_t preT[32];
+    uint16_t rowid[DD_MAXNA + 32];  // local row symbol -> composition id (query profile is rebuilt per strip)
     uint32_t win[64];       // sliding window of row records, slot = row & 63 (steady phase)
     union {
         struct {                 // while the pair is set up
@@ -47,34 +52,42 @@ struct DdWarpSmem {
 };
 #define DD_SMEM_BYTES (2048 + DD_WARPS * sizeof(DdWarpSmem))
 
-// columns per lane and number of column strips of a pair: the cheapest of 8, 12, 16 columns per lane
-__host__ __device__ inline void dd_plan(int l1, int l2, int &cpl, int &ns) {
+// Columns per lane (8, 12 or 16), number of column strips and table mode of a pair with l2 columns whose
+// reference-side profile uses `na` distinct compositions.  A query profile holds, for every row symbol,
+// the costs against the strip's 32*cpl columns laid out so that a lane finds its cpl bytes in one vector
+// load: na * 32 * cpl bytes, which bounds cpl by na.  Cost model in issued instructions: per strip and
+// wavefront step a fixed part plus cpl cells (fewer instructions per cell with a query profile).
+__host__ __device__ inline void dd_plan(int l2, int na, int &cpl, int &ns, bool &qp) {
     int best = 0x7fffffff;
     cpl = 16;
     ns = 1;
+    qp = false;
 #pragma unroll
-    for (int c = 16; c >= 8; c -= 4) {
-        const int n = (l2 + 32 * c - 1) / (32 * c);
-        const int cost = n * (c + DD_STEP_OV);  // x (l1 + 31) steps either way
-        if (cost < best) {
-            best = cost;
-            cpl = c;
-            ns = n;
+    for (int m = 1; m >= 0; --m)
+#pragma unroll
+        for (int c = 16; c >= 8; c -= 4) {
+            if (m == 1 && (na > DD_MAXNA || na * 32 * c > DD_TBYTES)) continue;
+            const int n = (l2 + 32 * c - 1) / (32 * c);
+            const int cost = n * (m ? (c * 8 + 40) : (c * 11 + 50));
+            if (cost < best) {
+                best = cost;
+                cpl = c;
+                ns = n;
+                qp = (m == 1);
+            }
         }
-    }
-    (void)l1;
 }
 
-// row record: bits 0..15 table row offset (local index * nb, or the id for the global table),
-// 16..23 gap cost d(0,l)
+// row record: bits 0..15 table row offset (query profile: local index * 32*cpl; compact table: local index *
+// nb; global table: the id), 16..23 gap cost d(0,l)
 __device__ __forceinline__ uint32_t dd_pack_row(int off, int gn) {
     return (uint32_t)off | ((uint32_t)(gn & 255) << 16);
 }
 
-// local alphabets, compact table, row records (same scheme as vsk_dp_kernel); returns nb, smemt
-__device__ __forceinline__ bool dd_setup(const uint16_t *__restrict__ L, const uint16_t *__restrict__ Tp, int l1, int l2,
-                                         const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
-                                         uint32_t *rowrec, int &nb_out) {
+// local alphabets, table mode, compact table, row records; returns the mode, nb and na
+__device__ __forceinline__ int dd_setup(const uint16_t *__restrict__ L, const uint16_t *__restrict__ Tp, int l1, int l2,
+                                        const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
+                                        uint32_t *rowrec, bool want_qp, int cpl, int &nb_out, int &na_out) {
     const int lane = threadIdx.x & 31;
     ws.bmL[lane] = 0;
     ws.bmT[lane] = 0;
@@ -98,8 +111,10 @@ __device__ __forceinline__ bool dd_setup(const uint16_t *__restrict__ L, const u
         if (lane >= o) { xl += a; xt += b; }
     }
     const int na = __shfl_sync(DD_FULL, xl, 31), nb = __shfl_sync(DD_FULL, xt, 31);
-    const bool smemt = (na <= 256) && (nb <= 256) && (na * nb <= DD_TBYTES);
-    if (smemt) {
+    int mode = DD_GLOBAL;
+    if (want_qp && na <= DD_MAXNA && na * 32 * cpl <= DD_TBYTES) mode = DD_QP;
+    else if ((na <= 256) && (nb <= 256) && (na * nb <= DD_TBYTES)) mode = DD_SMEMT;
+    if (mode != DD_GLOBAL) {
         ws.preT[lane] = (uint16_t)(xt - ct);
         uint32_t b = bl;
         int rk = xl - cl;
@@ -108,6 +123,7 @@ __device__ __forceinline__ bool dd_setup(const uint16_t *__restrict__ L, const u
             b &= b - 1;
             ws.u.su.mapL[id] = (uint8_t)rk;
             ws.u.su.invL[rk] = (uint16_t)id;
+            if (mode == DD_QP) ws.rowid[rk] = (uint16_t)id;
             ++rk;
         }
         b = bt;
@@ -119,31 +135,39 @@ __device__ __forceinline__ bool dd_setup(const uint16_t *__restrict__ L, const u
             ++rk;
         }
         __syncwarp();
+        if (mode == DD_SMEMT) {
 #pragma unroll 4
-        for (int a = 0; a < na; ++a) {
-            const uint8_t *drow = dist + (int)ws.u.su.invL[a] * VSK_DROW;
-            for (int c = lane; c < nb; c += 32) ws.T[a * nb + c] = __ldg(drow + ws.u.su.invT[c]);
+            for (int a = 0; a < na; ++a) {
+                const uint8_t *drow = dist + (int)ws.u.su.invL[a] * VSK_DROW;
+                for (int c = lane; c < nb; c += 32) ws.T[a * nb + c] = __ldg(drow + ws.u.su.invT[c]);
+            }
         }
         __syncwarp();
     }
+    const int rstride = (mode == DD_QP) ? 32 * cpl : nb;
     for (int i = lane; i < l1; i += 32) {
         const int id = L[i];
-        rowrec[i] = dd_pack_row(smemt ? (int)ws.u.su.mapL[id] * nb : id, s_gapnd[id]);
+        rowrec[i] = dd_pack_row(mode != DD_GLOBAL ? (int)ws.u.su.mapL[id] * rstride : id, s_gapnd[id]);
     }
     __syncwarp();
     nb_out = nb;
-    return smemt;
+    na_out = na;
+    return mode;
 }
 
-template <int CPL, bool SMEMT>
-__device__ __forceinline__ uint32_t dd_row_cells(int (&Hd)[CPL], const int (&tb)[CPL], const int (&gt)[CPL], int dgd,
-                                                 int lfd, const uint8_t *__restrict__ trow, int gl) {
+// One row of a lane's CPL cells.  Hin = the previous row of these columns, Hout = this row (the two may be
+// the same array).  q[] = the lane's bytes of the query profile row (MODE == DD_QP).
+template <int CPL, int MODE>
+__device__ __forceinline__ uint32_t dd_row_cells(const int (&Hin)[CPL], int (&Hout)[CPL], const int (&tb)[CPL],
+                                                 const int (&gt)[CPL], const uint32_t (&q)[CPL / 4], int dgd, int lfd,
+                                                 const uint8_t *__restrict__ trow, int gl) {
     uint32_t w = 0;
 #pragma unroll
     for (int j = 0; j < CPL; ++j) {
-        const int upd = Hd[j];
-        const int dlt = SMEMT ? (int)trow[tb[j]] : (int)__ldg(trow + tb[j]);
-        const int sa = dgd + dlt;   // diagonal
+        const int upd = Hin[j];
+        int sa;  // diagonal
+        if (MODE == DD_QP) sa = (int)__dp4a(q[j >> 2], 1u << (8 * (j & 3)), (unsigned)dgd);
+        else sa = dgd + (MODE == DD_SMEMT ? (int)trow[tb[j]] : (int)__ldg(trow + tb[j]));
         const int f = upd + gl;     // down
         const int e = lfd + gt[j];  // right
         // min3switch (profile.h:1098-1099): diag if sa<=f && sa<=e; else down if f<=e; else right.
@@ -152,7 +176,7 @@ __device__ __forceinline__ uint32_t dd_row_cells(int (&Hd)[CPL], const int (&tb)
         w = __funnelshift_l((uint32_t)(d - sa), w, 1);
         w = __funnelshift_l((uint32_t)(e - f), w, 1);
         dgd = upd;
-        Hd[j] = d;
+        Hout[j] = d;
         lfd = d;
     }
     return w;
@@ -167,10 +191,25 @@ __device__ __forceinline__ void dd_flush8(const DdWarpSmem &ws, int lane, uint32
     __stcs(dst + 1, b);
 }
 
-template <int CPL, bool SMEMT>
+// the lane's CPL bytes of a query profile row
+template <int CPL>
+__device__ __forceinline__ void dd_load_q(const uint8_t *p, uint32_t (&q)[CPL / 4]) {
+    if (CPL == 16) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(p);
+        q[0] = v.x; q[1] = v.y; q[2] = v.z; q[CPL / 4 - 1] = v.w;
+    } else if (CPL == 8) {
+        const uint2 v = *reinterpret_cast<const uint2 *>(p);
+        q[0] = v.x; q[CPL / 4 - 1] = v.y;
+    } else {
+#pragma unroll
+        for (int k = 0; k < CPL / 4; ++k) q[k] = reinterpret_cast<const uint32_t *>(p)[k];
+    }
+}
+
+template <int CPL, int MODE>
 __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *__restrict__ Tp,
                                         const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
-                                        int nb, int *bscr, const uint32_t *rowrec, uint32_t *__restrict__ dir,
+                                        int na, int *bscr, const uint32_t *rowrec, uint32_t *__restrict__ dir,
                                         int4 *out) {
     const int lane = threadIdx.x & 31;
     const int l1 = job.l1, l2 = job.l2, br = job.br;
@@ -180,6 +219,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
     int totd = 0;
     int Hd[CPL];
     int prev_r_hi = l1;
+    const uint8_t *qlane = ws.T + lane * CPL;  // this lane's bytes inside a query profile row
 
     for (int pass = 0; pass < npass; ++pass) {
         const int cbase = pass * (32 * CPL) + lane * CPL;
@@ -191,7 +231,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             const int id = (c < l2) ? (int)Tp[c] : 0;
             const int g = s_gapnd[id] & 255;
             gt[j] = g;
-            if (SMEMT) {
+            if (MODE == DD_SMEMT) {
                 const int w = id >> 5;
                 tb[j] = ws.preT[w] + __popc(ws.bmT[w] & ((1u << (id & 31)) - 1u));
             } else {
@@ -199,6 +239,22 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             }
             sd += g;
             Hd[j] = sd;
+        }
+        if (MODE == DD_QP) {
+            // query profile of this strip: row symbol a, this lane's columns -> CPL bytes at a*32*CPL + lane*CPL
+            // (the previous strip's sweep is over: every lane passed the __syncwarp at the end of the loop body)
+            for (int a = 0; a < na; ++a) {
+                const uint8_t *drow = dist + (int)ws.rowid[a] * VSK_DROW;
+                uint32_t wds[CPL / 4];
+#pragma unroll
+                for (int k = 0; k < CPL / 4; ++k) wds[k] = 0;
+#pragma unroll
+                for (int j = 0; j < CPL; ++j) wds[j >> 2] |= (uint32_t)__ldg(drow + tb[j]) << (8 * (j & 3));
+                uint32_t *dstw = reinterpret_cast<uint32_t *>(ws.T + a * (32 * CPL) + lane * CPL);
+#pragma unroll
+                for (int k = 0; k < CPL / 4; ++k) dstw[k] = wds[k];
+            }
+            __syncwarp();
         }
         int xd = sd;
 #pragma unroll
@@ -246,7 +302,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             const uint32_t rec = rec_next;
             rec_next = __ldcg(rowrec + min(max(r + 1, 0), l1 - 1));
             const int gl = (int)(rec >> 16);
-            const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
+            const uint8_t *trow = (MODE == DD_SMEMT) ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
             if (active) {
                 if (lane == 0) {
                     if (pass == 0) {
@@ -256,7 +312,9 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                         nxt = (r + 1 < prev_r_hi) ? __ldcg(bscr + r + 1) : VSK_BIG;
                     }
                 }
-                const uint32_t w = dd_row_cells<CPL, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl);
+                uint32_t q[CPL / 4];
+                if (MODE == DD_QP) dd_load_q<CPL>(qlane + (rec & 0xffffu), q);
+                const uint32_t w = dd_row_cells<CPL, MODE>(Hd, Hd, tb, gt, q, dgd, lfd, trow, gl);
                 dgd = lfd;
                 ws.u.ring[lane][r & 15] = w;
                 if (wr_scratch) bscr[r] = Hd[CPL - 1];
@@ -283,17 +341,22 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             uint32_t wpre = 0;
             __syncwarp();
             rec_next = ws.win[(s - lane) & 63];
-            for (int k = 0; s < r_hi; ++s, ++k) {
+            int k = 0;
+            // one steady step: previous row of the lane's columns in Hin, this row into Hout.  The loop
+            // below runs it twice per trip with the two arrays swapping roles, so no row is copied.
+            auto steady = [&](const int (&Hin)[CPL], int (&Hout)[CPL]) {
                 const int r = s - lane;
                 if ((k & 31) == 0) {  // rows s+33 .. s+64: needed from step s+32 on
                     wpre = __ldcg(rowrec + s + 33 + lane);
                     if (pass > 0) bpre = __ldcg(bscr + s + 33 + lane);
                 }
-                int lfd = __shfl_up_sync(DD_FULL, Hd[CPL - 1], 1);
+                int lfd = __shfl_up_sync(DD_FULL, Hin[CPL - 1], 1);
                 const uint32_t rec = rec_next;
                 rec_next = ws.win[(r + 1) & 63];
                 const int gl = (int)(rec >> 16);
-                const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
+                const uint8_t *trow = (MODE == DD_SMEMT) ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
+                uint32_t q[CPL / 4];
+                if (MODE == DD_QP) dd_load_q<CPL>(qlane + (rec & 0xffffu), q);
                 if (pass == 0) {
                     if (lane == 0) lfd = dgd + gl;  // column 0, profile.h:2084-2090
                 } else {
@@ -301,10 +364,10 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                     if (lane == 0) lfd = nxt;
                     nxt = (s + 1 < prev_r_hi) ? v : VSK_BIG;
                 }
-                const uint32_t w = dd_row_cells<CPL, SMEMT>(Hd, tb, gt, dgd, lfd, trow, gl);
+                const uint32_t w = dd_row_cells<CPL, MODE>(Hin, Hout, tb, gt, q, dgd, lfd, trow, gl);
                 dgd = lfd;
                 ws.u.ring[lane][r & 15] = w;
-                if (wr_scratch) *bp = Hd[CPL - 1];
+                if (wr_scratch) *bp = Hout[CPL - 1];
                 ++bp;
                 if ((s & 7) == 7) {  // the lane's last complete group of 8 rows goes out
                     const int g0 = ((r + 1) & ~7) - 8;
@@ -316,6 +379,18 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                     bcur = bpre;
                     __syncwarp();
                 }
+                ++s;
+                ++k;
+            };
+            int Hx[CPL];
+            while (s + 1 < r_hi) {
+                steady(Hd, Hx);
+                steady(Hx, Hd);
+            }
+            if (s < r_hi) {
+                steady(Hd, Hx);
+#pragma unroll
+                for (int j = 0; j < CPL; ++j) Hd[j] = Hx[j];
             }
         }
         for (; s < r_hi + 31; ++s) step(s, true);
@@ -336,13 +411,14 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
     }
 }
 
-// forward sweep: jobs[0..n) with their direction-word offsets dir_off[] into dirbuf
-__global__ void __maxnreg__(120)
+// forward sweep: jobs[0..n) with their direction-word offsets dir_off[] into dirbuf and their plan bytes
+// (columns per lane | 0x80 = query profile) from vsk_dd_plan_kernel
+__global__ void __launch_bounds__(DD_WARPS * 32, 2)
 vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
                   const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
-                  const int *__restrict__ bounds, int batch, int64_t batch_words, int job_end,
-                  const uint8_t *__restrict__ dist, const uint16_t *__restrict__ gapnd, int *scratch, int scratch_stride,
-                  uint32_t *__restrict__ dirbuf, int *queue, int4 *out) {
+                  const uint8_t *__restrict__ plan, const int *__restrict__ bounds, int batch, int64_t batch_words,
+                  int job_end, const uint8_t *__restrict__ dist, const uint16_t *__restrict__ gapnd, int *scratch,
+                  int scratch_stride, uint32_t *__restrict__ dirbuf, int *queue, int4 *out) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -362,15 +438,16 @@ vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restr
         if (!VSK_DP_DIRJOB(job.l2)) continue;
         const uint16_t *L = left_ids + job.left_off;
         const uint16_t *Tp = top_ids + job.top_off;
-        int nb = 0;
-        const bool smemt = dd_setup(L, Tp, job.l1, job.l2, dist, s_gapnd, ws, my_rowrec, nb);
+        const int pl = plan[ji];
+        const int cpl = pl & 0x7f;
+        int nb = 0, na = 0;
+        const int mode = dd_setup(L, Tp, job.l1, job.l2, dist, s_gapnd, ws, my_rowrec, (pl & 0x80) != 0, cpl, nb, na);
         uint32_t *dir = dirbuf + (dir_off[ji] - (int64_t)batch * batch_words);
-        int cpl, ns;
-        dd_plan(job.l1, job.l2, cpl, ns);
-#define DD_DISPATCH(C)                                                                       \
-    do {                                                                                     \
-        if (smemt) dd_pair<C, true>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out); \
-        else dd_pair<C, false>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out);      \
+#define DD_DISPATCH(C)                                                                                        \
+    do {                                                                                                      \
+        if (mode == DD_QP) dd_pair<C, DD_QP>(job, Tp, dist, s_gapnd, ws, na, my_bscr, my_rowrec, dir, out);   \
+        else if (mode == DD_SMEMT) dd_pair<C, DD_SMEMT>(job, Tp, dist, s_gapnd, ws, na, my_bscr, my_rowrec, dir, out); \
+        else dd_pair<C, DD_GLOBAL>(job, Tp, dist, s_gapnd, ws, na, my_bscr, my_rowrec, dir, out);             \
     } while (0)
         if (cpl == 16) DD_DISPATCH(16);
         else if (cpl == 12) DD_DISPATCH(12);
@@ -437,7 +514,8 @@ __device__ __forceinline__ void dq_pair(const vsk_dp_job &job, const uint16_t *_
         const uint8_t *trow = s_ktab + (int)s_dense[id] * K;
         if (active) {
             if (glane == 0) lfd = dgd + gl;  // column 0, profile.h:2084-2090
-            const uint32_t w = dd_row_cells<CPL, true>(Hd, tb, gt, dgd, lfd, trow, gl);
+            const uint32_t qnone[CPL / 4] = {};
+            const uint32_t w = dd_row_cells<CPL, DD_SMEMT>(Hd, Hd, tb, gt, qnone, dgd, lfd, trow, gl);
             dgd = lfd;
             ring[r & 15] = w;
         }
@@ -530,9 +608,9 @@ vsk_dp_q8dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
 __global__ void __launch_bounds__(DT_THREADS)
 vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
                     const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
-                    const int *__restrict__ bounds, int batch, int64_t batch_words, const uint8_t *__restrict__ dist,
-                    const uint16_t *__restrict__ gapnd, const uint32_t *__restrict__ dirbuf, int4 *out,
-                    vsk_dp_job *redo, int *redo_count, int q_begin) {
+                    const uint8_t *__restrict__ plan, const int *__restrict__ bounds, int batch, int64_t batch_words,
+                    const uint8_t *__restrict__ dist, const uint16_t *__restrict__ gapnd,
+                    const uint32_t *__restrict__ dirbuf, int4 *out, vsk_dp_job *redo, int *redo_count, int q_begin) {
     __shared__ uint16_t s_gapnd[1024];
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_gapnd[i] = gapnd[i];
     __syncthreads();
@@ -550,9 +628,7 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
         const uint16_t *Tp = top_ids + job.top_off;
         const uint32_t *dir = dirbuf + (off0 - (int64_t)batch * batch_words);
         const int l1p = (job.l1 + 7) & ~7;
-        int cpl, ns;
-        if (ji >= q_begin) cpl = dq_cpl(job.l2);  // 8-lane job
-        else dd_plan(job.l1, job.l2, cpl, ns);
+        const int cpl = (ji >= q_begin) ? dq_cpl(job.l2) : (plan[ji] & 0x7f);  // 8-lane job : sweep's plan
         int r = job.l1, c = job.l2;
         int p1 = 0, sumw = 0, len = 0;
         // position of column c-1 inside the strips: strip*32 + lane, cell
@@ -637,20 +713,55 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
     }
 }
 
-// direction words a job needs (0 = not a job for this path); jobs[q_begin..n) are the 8-lane jobs
-__global__ void vsk_dd_words_kernel(const vsk_dp_job *__restrict__ jobs, int n, int q_begin,
-                                    int64_t *__restrict__ words) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+// Plan + direction words of the warp-per-pair jobs [0, n_warp): one warp per job counts the distinct
+// compositions of the reference-side profile (that bounds the columns per lane a query profile allows),
+// dd_plan picks columns per lane / strips / table mode; plan[i] = cpl | 0x80 (query profile), words[i] = the
+// direction words the job needs (0 = not a job for this path).
+__global__ void __launch_bounds__(256)
+vsk_dd_plan_kernel(const uint16_t *__restrict__ left_ids, const vsk_dp_job *__restrict__ jobs, int n_warp,
+                   int64_t *__restrict__ words, uint8_t *__restrict__ plan, int force) {
+    __shared__ uint32_t s_bm[8][32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int i = blockIdx.x * 8 + warp;
+    if (i >= n_warp) return;
     const int l1 = jobs[i].l1, l2 = jobs[i].l2;
-    const int64_t l1p = (l1 + 7) & ~7;
-    if (i >= q_begin) {
-        words[i] = DQ_G * l1p;
+    if (!VSK_DP_DIRJOB(l2)) {
+        if (lane == 0) { words[i] = 0; plan[i] = 0; }
         return;
     }
-    int cpl, ns;
-    dd_plan(l1, l2, cpl, ns);
-    words[i] = VSK_DP_DIRJOB(l2) ? (int64_t)ns * 32 * l1p : 0;
+    s_bm[warp][lane] = 0;
+    __syncwarp();
+    const uint16_t *L = left_ids + jobs[i].left_off;
+    for (int k = lane; k < l1; k += 32) {
+        const int id = L[k];
+        atomicOr(&s_bm[warp][id >> 5], 1u << (id & 31));
+    }
+    __syncwarp();
+    int na = __popc(s_bm[warp][lane]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) na += __shfl_xor_sync(DD_FULL, na, o);
+    if (lane == 0) {
+        int cpl, ns;
+        bool qp;
+        dd_plan(l2, na, cpl, ns, qp);
+        if (force) {  // tuning aid (VSK_DD_FORCE): columns per lane and table mode as told, where the alphabet allows
+            cpl = force & 0x7f;
+            ns = (l2 + 32 * cpl - 1) / (32 * cpl);
+            qp = (force & 0x80) && na <= DD_MAXNA && na * 32 * cpl <= DD_TBYTES;
+        }
+        const int64_t l1p = (l1 + 7) & ~7;
+        words[i] = (int64_t)ns * 32 * l1p;
+        plan[i] = (uint8_t)(cpl | (qp ? 0x80 : 0));
+    }
+}
+
+// direction words of the 8-lane jobs [q_begin, n)
+__global__ void vsk_dd_words8_kernel(const vsk_dp_job *__restrict__ jobs, int n, int q_begin,
+                                     int64_t *__restrict__ words) {
+    const int i = q_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t l1p = (jobs[i].l1 + 7) & ~7;
+    words[i] = DQ_G * l1p;
 }
 
 // bounds[b] = first job whose direction words start at or after b*batch_words (jobs of a batch are
@@ -719,10 +830,26 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     if ((rc = dd_reserve(ctx, 0, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_words))) return rc;
     if ((rc = dd_reserve(ctx, 1, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_off))) return rc;
     if ((rc = dd_reserve(ctx, 2, tmp_bytes + 16, &d_tmp))) return rc;
+    uint8_t *d_plan = nullptr;
+    if ((rc = dd_reserve(ctx, 7, (size_t)n + 16, (void **)&d_plan))) return rc;
     VSK_CUDA(ctx, cudaStreamWaitEvent(s0, ctx->dd_ev[0], 0));
     VSK_CUDA(ctx, cudaMemsetAsync(d_words + n, 0, sizeof(int64_t), s0));
-    vsk_dd_words_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s0>>>(d_jobs, (int)n, (int)n_warp, d_words);
-    ctx->launches++;
+    if (n_warp > 0) {
+        static const int force = [] {  // e.g. VSK_DD_FORCE=qp16, t12 (tuning aid)
+            const char *e = getenv("VSK_DD_FORCE");
+            if (!e || !*e) return 0;
+            const bool qp = (e[0] == 'q');
+            const int c = atoi(e + (qp ? 2 : 1));
+            return (c == 8 || c == 12 || c == 16) ? (c | (qp ? 0x80 : 0)) : 0;
+        }();
+        vsk_dd_plan_kernel<<<(unsigned)((n_warp + 7) / 8), 256, 0, s0>>>(d_left_ids, d_jobs, (int)n_warp, d_words, d_plan,
+                                                                        force);
+        ctx->launches++;
+    }
+    if (n_q8 > 0) {
+        vsk_dd_words8_kernel<<<(unsigned)((n_q8 + 255) / 256), 256, 0, s0>>>(d_jobs, (int)n, (int)n_warp, d_words);
+        ctx->launches++;
+    }
     VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
     ctx->launches += 2;
     int64_t total = 0, off_q8 = 0;  // all words; words before the first 8-lane job
@@ -801,9 +928,9 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
                 VSK_CUDA(ctx, cudaEventCreate(&pe1));
                 VSK_CUDA(ctx, cudaEventRecord(pe0, st));
             }
-            vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, dd_smem, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
-                                                                    batch_words, (int)n_warp, ctx->d_dist, ctx->d_gapnd,
-                                                                    scr, stride, dir, d_queue, d_out);
+            vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, dd_smem, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_plan, d_bounds,
+                                                                    b, batch_words, (int)n_warp, ctx->d_dist,
+                                                                    ctx->d_gapnd, scr, stride, dir, d_queue, d_out);
             ctx->launches++;
             if (ctx->profile) {
                 VSK_CUDA(ctx, cudaEventRecord(pe1, st));
@@ -817,9 +944,10 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
                 ctx->d_tiny_ktab, K, ctx->d_gapnd, dir, d_queue8 + b, d_out);
             ctx->launches++;
         }
-        vsk_dp_trace_kernel<<<ctx->sm_count * 16, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
-                                                                       batch_words, ctx->d_dist, ctx->d_gapnd, dir,
-                                                                       d_out, *redo, *redo_count, (int)n_warp);
+        vsk_dp_trace_kernel<<<ctx->sm_count * 16, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_plan,
+                                                                       d_bounds, b, batch_words, ctx->d_dist,
+                                                                       ctx->d_gapnd, dir, d_out, *redo, *redo_count,
+                                                                       (int)n_warp);
         ctx->launches++;
     }
     VSK_CUDA(ctx, cudaGetLastError());

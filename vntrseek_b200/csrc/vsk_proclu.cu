@@ -1329,11 +1329,18 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         if (prm->key_budget <= 0)
             if (const char *e = getenv("VSK_KEY_BUDGET")) budget = std::max<int64_t>(1024, atoll(e));
         int32_t pb = 0;
+        int64_t masters_total = 0, masters_done = 0;
+        if (prm->progress)
+            for (int32_t q = 0; q < hq->n; ++q) masters_total += hq->master[(size_t)q] ? 1 : 0;
         while (pb < nprof && rc == VSK_OK) {
             int32_t pe = pb + 2;
             while (pe < nprof && hoff[(size_t)pe + 2] - hoff[(size_t)pb] <= budget) pe += 2;
             rc = run_chunk(ctx, R, Q, prm, pb, pe, off, hoff[(size_t)pb], hoff[(size_t)pe] - hoff[(size_t)pb], wcache, res);
             res->stats.chunks++;
+            if (prm->progress && rc == VSK_OK) {
+                for (int32_t q = pb / 2; q < pe / 2; ++q) masters_done += hq->master[(size_t)q] ? 1 : 0;
+                prm->progress(prm->progress_user, masters_done, masters_total, res->stats.profile_alignments);
+            }
             pb = pe;
         }
     }
