@@ -165,6 +165,14 @@ int vsk_ed_pairs(vsk_ctx *ctx, const char *text, const int64_t *t_off, const int
 typedef struct vsk_trset vsk_trset;
 int vsk_trset_load_leb36(const char *path, int is_read, int maxflank, int option_r, int reflen,
                          vsk_trset **out);
+/* The same with the parsed arrays kept in a binary file: parsing the text
+ * (LEB36 digits, consensus, flank clean-up: profile.h:448-732,786-807) costs about 2 us per record
+ * per core, more than the GPU scan costs per read.  cache_path (NULL = no cache) is read when it
+ * was written for exactly this text file (size, modification time, hash of its first and last
+ * 64 KB) and these parse parameters, else the text is parsed and the file (re)written through a
+ * temporary + rename.  The redundancy state is not cached: apply the .rotindex afterwards as usual. */
+int vsk_trset_load_leb36_cached(const char *path, int is_read, int maxflank, int option_r, int reflen,
+                                const char *cache_path, vsk_trset **out, int *from_cache);
 /* same from arrays: prof_off[2n+1] into ids; flank_off[2n+1] into flanks (left,
  * right per record, as they stand in the file: left NOT reversed)             */
 int vsk_trset_from_arrays(int32_t n, const int32_t *key, const int32_t *patlen,

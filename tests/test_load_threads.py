@@ -89,3 +89,44 @@ def test_bad_composition_id_is_an_error_either_way(big_file, tmp_path):
     for t in (1, 4):
         with pytest.raises(v.VskError):
             _load(p, t)
+
+
+def test_packed_cache_serves_the_same_set(tmp_path):
+    """vsk_trset_load_leb36_cached: the first load parses the text and writes the binary file, the second
+    reads it back (same checksum, also after the rotindex), a changed text file or other parse parameters
+    are not served from it, a damaged file is ignored and replaced"""
+    import os
+    import time
+
+    import vntrseek_b200 as v
+    from vntrseek_b200 import synth
+    refs = synth.make_refs(300, seed=8, max_patlen=400, rot_frac=0.05)
+    reads = synth.make_reads(refs, 500, seed=108, rot_frac=0.03)
+    path = str(tmp_path / "reads.leb36")
+    reads.write_leb36(path)
+    cache = path + ".vsktr"
+    plain = v.TRSetHandle.from_file(path, is_read=True, maxflank=50)
+    a = v.TRSetHandle.from_file(path, is_read=True, maxflank=50, cache_path=cache)
+    assert a.from_cache is False and os.path.getsize(cache) > 1000
+    b = v.TRSetHandle.from_file(path, is_read=True, maxflank=50, cache_path=cache)
+    assert b.from_cache is True
+    assert plain.checksum() == a.checksum() == b.checksum()
+    assert len(b) == 500
+    # other parse parameters: the cut of the read flanks is baked into the arrays
+    c = v.TRSetHandle.from_file(path, is_read=True, maxflank=20, cache_path=cache)
+    assert c.from_cache is False
+    assert c.checksum() == v.TRSetHandle.from_file(path, is_read=True, maxflank=20).checksum() != plain.checksum()
+    # the text changes (one record less): not served
+    time.sleep(0.01)
+    lines = open(path).read().splitlines()
+    open(path, "w").write("\n".join(lines[:-1]) + "\n")
+    d = v.TRSetHandle.from_file(path, is_read=True, maxflank=20, cache_path=cache, rotindex=False)
+    assert d.from_cache is False and len(d) == 499
+    # damaged file
+    blob = open(cache, "rb").read()
+    open(cache, "wb").write(blob[: len(blob) // 2])
+    e = v.TRSetHandle.from_file(path, is_read=True, maxflank=20, cache_path=cache, rotindex=False)
+    assert e.from_cache is False and e.checksum() == d.checksum()
+    f = v.TRSetHandle.from_file(path, is_read=True, maxflank=20, cache_path=cache, rotindex=False)
+    assert f.from_cache is True and f.checksum() == d.checksum()
+    assert not [x for x in os.listdir(str(tmp_path)) if ".tmp" in x]

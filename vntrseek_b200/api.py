@@ -195,12 +195,20 @@ class TRSetHandle:
         self.h = h
 
     @classmethod
-    def from_file(cls, path, is_read, maxflank=50, option_r=0, reflen=50, rotindex=True):
+    def from_file(cls, path, is_read, maxflank=50, option_r=0, reflen=50, rotindex=True, cache_path=None):
+        """cache_path: keep / use the parsed arrays in that binary file (vsk_trset_load_leb36_cached);
+        `.from_cache` tells whether the text was parsed (False) or the file served (True)"""
         h = C.c_void_p()
-        rc = lib().vsk_trset_load_leb36(path.encode(), int(is_read), maxflank, option_r, reflen, C.byref(h))
+        hit = C.c_int(0)
+        if cache_path:
+            rc = lib().vsk_trset_load_leb36_cached(path.encode(), int(is_read), maxflank, option_r, reflen,
+                                                   os.fsencode(cache_path), C.byref(h), C.byref(hit))
+        else:
+            rc = lib().vsk_trset_load_leb36(path.encode(), int(is_read), maxflank, option_r, reflen, C.byref(h))
         if rc != 0:
             raise VskError(f"cannot load {path} ({rc})")
         ts = cls(h)
+        ts.from_cache = bool(hit.value)
         if rotindex:
             ts.apply_rotindex(path + ".rotindex")
         return ts
@@ -237,6 +245,9 @@ class TRSetHandle:
         if lib().vsk_trset_pin(self.h) != 0:
             raise VskError("vsk_trset_pin failed")
         return self
+
+    def checksum(self):
+        return lib().vsk_trset_checksum(self.h)
 
     def __len__(self):
         return lib().vsk_trset_size(self.h)

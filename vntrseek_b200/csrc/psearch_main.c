@@ -22,6 +22,18 @@ static void die(const char *msg) {
     exit(1);
 }
 
+/* VSK_TRSET_CACHE=1: keep the parsed arrays of every .leb36 file in <file>.vsktr next to it (read
+ * back when the text has not changed since); unset = parse the text in every process as the reference does */
+static int load_profiles(const char *path, int is_read, int maxflank, int option_r, int reflen, vsk_trset **out) {
+    const char *e = getenv("VSK_TRSET_CACHE");
+    if (e && *e && strcmp(e, "0") != 0) {
+        char cache[1200];
+        snprintf(cache, sizeof cache, "%s.vsktr", path);
+        return vsk_trset_load_leb36_cached(path, is_read, maxflank, option_r, reflen, cache, out, NULL);
+    }
+    return vsk_trset_load_leb36(path, is_read, maxflank, option_r, reflen, out);
+}
+
 /* The reference's per-percent progress lines (psearch.c:836-844): "\nP% (ProfileAlignments: N, total
  * time: T secs)", one for every percent of the scan list, P counting up from 0.  The scan runs chunk by
  * chunk on the GPU, so the lines of all the marks a chunk crosses appear together when it ends, each with
@@ -134,12 +146,12 @@ int main(int argc, char **argv) {
     }
 
     fprintf(stderr, "\nReading reference profiles...");
-    if (vsk_trset_load_leb36(argv[1], 0, maxflank, option_r, reflen, &refs) != VSK_OK)
+    if (load_profiles(argv[1], 0, maxflank, option_r, reflen, &refs) != VSK_OK)
         die(refs ? vsk_trset_error(refs) : "unable to read reference profiles");
     fprintf(stderr, "(total time: %.1lf secs)", (double) (time(NULL) - startTime));
     fprintf(stderr, "\nLoaded %d profiles from reference file!", (int) vsk_trset_size(refs));
     fprintf(stderr, "\nReading read profiles...");
-    if (vsk_trset_load_leb36(argv[2], 1, maxflank, option_r, reflen, &reads) != VSK_OK)
+    if (load_profiles(argv[2], 1, maxflank, option_r, reflen, &reads) != VSK_OK)
         die(reads ? vsk_trset_error(reads) : "unable to read read profiles");
     fprintf(stderr, "(total time: %.1lf secs)", (double) (time(NULL) - startTime));
     fprintf(stderr, "\nLoaded %d profiles from reads file!", (int) vsk_trset_size(reads));

@@ -21,15 +21,16 @@
 // eighth step all lanes store their last complete group of 8 rows as one sector.
 #include <algorithm>
 #include <cstdlib>
+#include <type_traits>
 
 #include <cub/cub.cuh>
 
 #include "vsk_internal.cuh"
 
 #define DD_WARPS 4
-#define DD_TBYTES 24576  // per warp: query profile of a strip [row symbol][lane][CPL], or the compact table [na][nb]
+#define DD_TBYTES 8192   // per warp: compact table [na][nb], or the query profile of a strip [row symbol][lane][CPL]
 #define DD_MAXCPL 16
-#define DD_MAXNA 96      // row alphabets up to this size can have a query profile (at 8 columns per lane)
+#define DD_MAXNA 32      // row alphabets up to this size can have a query profile (at 8 columns per lane)
 #define DD_FULL 0xffffffffu
 // how the sweep finds d(row symbol, column symbol)
 #define DD_GLOBAL 0  // one byte load per cell from the symmetric table in global memory
@@ -126,8 +127,8 @@ __device__ __forceinline__ int dd_setup(const uint16_t *__restrict__ L, const ui
             if (mode == DD_QP) ws.rowid[rk] = (uint16_t)id;
             ++rk;
         }
-        b = bt;
-        rk = xt - ct;
+        b = (mode == DD_SMEMT) ? bt : 0u;  // column symbols by rank: the compact table only (nb <= 256 there;
+        rk = xt - ct;                       // a query profile is indexed by column position, whatever nb is)
         while (b) {
             const int id = lane * 32 + __ffs(b) - 1;
             b &= b - 1;
@@ -344,11 +345,12 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             int k = 0;
             // one steady step: previous row of the lane's columns in Hin, this row into Hout.  The loop
             // below runs it twice per trip with the two arrays swapping roles, so no row is copied.
-            auto steady = [&](const int (&Hin)[CPL], int (&Hout)[CPL]) {
+            auto steady = [&](auto first_c, const int (&Hin)[CPL], int (&Hout)[CPL]) {
+                constexpr bool FIRST = decltype(first_c)::value;  // first strip: column 0 instead of a previous strip
                 const int r = s - lane;
                 if ((k & 31) == 0) {  // rows s+33 .. s+64: needed from step s+32 on
                     wpre = __ldcg(rowrec + s + 33 + lane);
-                    if (pass > 0) bpre = __ldcg(bscr + s + 33 + lane);
+                    if (!FIRST) bpre = __ldcg(bscr + s + 33 + lane);
                 }
                 int lfd = __shfl_up_sync(DD_FULL, Hin[CPL - 1], 1);
                 const uint32_t rec = rec_next;
@@ -357,7 +359,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                 const uint8_t *trow = (MODE == DD_SMEMT) ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
                 uint32_t q[CPL / 4];
                 if (MODE == DD_QP) dd_load_q<CPL>(qlane + (rec & 0xffffu), q);
-                if (pass == 0) {
+                if (FIRST) {
                     if (lane == 0) lfd = dgd + gl;  // column 0, profile.h:2084-2090
                 } else {
                     const int v = __shfl_sync(DD_FULL, bcur, k & 31);  // previous strip's last cell of row s+1
@@ -383,14 +385,28 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                 ++k;
             };
             int Hx[CPL];
-            while (s + 1 < r_hi) {
-                steady(Hd, Hx);
-                steady(Hx, Hd);
-            }
-            if (s < r_hi) {
-                steady(Hd, Hx);
+            if (pass == 0) {
+                const std::true_type first;
+                while (s + 1 < r_hi) {
+                    steady(first, Hd, Hx);
+                    steady(first, Hx, Hd);
+                }
+                if (s < r_hi) {
+                    steady(first, Hd, Hx);
 #pragma unroll
-                for (int j = 0; j < CPL; ++j) Hd[j] = Hx[j];
+                    for (int j = 0; j < CPL; ++j) Hd[j] = Hx[j];
+                }
+            } else {
+                const std::false_type later;
+                while (s + 1 < r_hi) {
+                    steady(later, Hd, Hx);
+                    steady(later, Hx, Hd);
+                }
+                if (s < r_hi) {
+                    steady(later, Hd, Hx);
+#pragma unroll
+                    for (int j = 0; j < CPL; ++j) Hd[j] = Hx[j];
+                }
             }
         }
         for (; s < r_hi + 31; ++s) step(s, true);
@@ -413,7 +429,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
 
 // forward sweep: jobs[0..n) with their direction-word offsets dir_off[] into dirbuf and their plan bytes
 // (columns per lane | 0x80 = query profile) from vsk_dd_plan_kernel
-__global__ void __launch_bounds__(DD_WARPS * 32, 2)
+__global__ void __maxnreg__(120)
 vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
                   const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
                   const uint8_t *__restrict__ plan, const int *__restrict__ bounds, int batch, int64_t batch_words,

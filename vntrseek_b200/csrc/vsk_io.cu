@@ -6,6 +6,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <thread>
@@ -440,4 +442,141 @@ extern "C" uint64_t vsk_trset_checksum(const vsk_trset *ts) {
     mix(ts->dir.data(), ts->dir.size());
     for (const auto &r : ts->rotlist) mix(r.data(), r.size() * 4);
     return h;
+}
+
+// ---- packed TR sets ----------------------------------------------------------------------
+// With the scan on the GPU and the seed index cached, reading the .leb36 TEXT is the slowest step
+// of a psearch process (ReadProfileWithRC, profile.h:448-732: about 2 us per record per core --
+// LEB36 digits, consensus, flank clean-up -- against 0.35 us per read for the scan).  The arrays
+// that parse produces are kept in a binary file next to the text: magic, the parse parameters, a
+// fingerprint of the text file (size, modification time, hash of its first and last 64 KB), the
+// arrays, an end mark.  A file that does not match in any of these is ignored and rewritten.  The
+// redundancy state (.rotindex) is not part of it: vsk_trset_apply_rotindex runs after either load.
+static const char kTrsMagic[8] = {'V', 'S', 'K', 'T', 'R', 'S', '1', 0};
+static const uint64_t kTrsEnd = 0x444e455352544b53ull;
+
+struct TrsHeader {
+    char magic[8];
+    int32_t is_read, maxflank, option_r, reflen;
+    uint64_t src_size, src_mtime_ns, src_hash;
+    int64_t n;
+};
+
+static bool source_fingerprint(const char *path, TrsHeader &h) {
+    struct stat st;
+    if (stat(path, &st) != 0) return false;
+    h.src_size = (uint64_t)st.st_size;
+    h.src_mtime_ns = (uint64_t)st.st_mtim.tv_sec * 1000000000ull + (uint64_t)st.st_mtim.tv_nsec;
+    FILE *f = fopen(path, "rb");
+    if (!f) return false;
+    std::vector<uint8_t> buf(1 << 16);
+    uint64_t hash = 0xcbf29ce484222325ull;
+    auto mix = [&](size_t got) {
+        for (size_t i = 0; i < got; ++i) hash = (hash ^ buf[i]) * 0x100000001b3ull;
+    };
+    mix(fread(buf.data(), 1, buf.size(), f));
+    if (st.st_size > (off_t)buf.size()) {
+        fseek(f, -(long)buf.size(), SEEK_END);
+        mix(fread(buf.data(), 1, buf.size(), f));
+    }
+    fclose(f);
+    h.src_hash = hash;
+    return true;
+}
+
+template <typename T>
+static bool trs_put(FILE *f, const std::vector<T> &v) {
+    const uint64_t n = v.size();
+    return fwrite(&n, sizeof n, 1, f) == 1 && (n == 0 || fwrite(v.data(), sizeof(T), n, f) == n);
+}
+template <typename T>
+static bool trs_get(FILE *f, std::vector<T> &v, uint64_t limit) {
+    uint64_t n = 0;
+    if (fread(&n, sizeof n, 1, f) != 1 || n > limit) return false;
+    v.resize(n);
+    return n == 0 || fread(v.data(), sizeof(T), n, f) == n;
+}
+
+static int trset_save_packed(const vsk_trset &ts, const TrsHeader &h, const char *path) {
+    const std::string tmp = std::string(path) + ".tmp" + std::to_string((long long)getpid());
+    FILE *f = fopen(tmp.c_str(), "wb");
+    if (!f) return VSK_ERR_ARG;
+    bool ok = fwrite(&h, sizeof h, 1, f) == 1 && trs_put(f, ts.key) && trs_put(f, ts.patlen) && trs_put(f, ts.prof_off) &&
+              trs_put(f, ts.ids) && trs_put(f, ts.cons_off) && trs_put(f, ts.cons) && trs_put(f, ts.fl_off) &&
+              trs_put(f, ts.fl) && trs_put(f, ts.leftlen) && trs_put(f, ts.rightlen) && fwrite(&kTrsEnd, 8, 1, f) == 1;
+    ok = (fclose(f) == 0) && ok;
+    if (!ok || rename(tmp.c_str(), path) != 0) {
+        remove(tmp.c_str());
+        return VSK_ERR_ARG;
+    }
+    return VSK_OK;
+}
+
+static vsk_trset *trset_load_packed(const TrsHeader &want, const char *path) {
+    FILE *f = fopen(path, "rb");
+    if (!f) return nullptr;
+    fseek(f, 0, SEEK_END);
+    const uint64_t limit = (uint64_t)ftell(f);
+    fseek(f, 0, SEEK_SET);
+    TrsHeader h;
+    vsk_trset *ts = new vsk_trset();
+    uint64_t end = 0;
+    bool ok = fread(&h, sizeof h, 1, f) == 1 && memcmp(&h, &want, sizeof h) == 0 && trs_get(f, ts->key, limit) &&
+              trs_get(f, ts->patlen, limit) && trs_get(f, ts->prof_off, limit) && trs_get(f, ts->ids, limit) &&
+              trs_get(f, ts->cons_off, limit) && trs_get(f, ts->cons, limit) && trs_get(f, ts->fl_off, limit) &&
+              trs_get(f, ts->fl, limit) && trs_get(f, ts->leftlen, limit) && trs_get(f, ts->rightlen, limit) &&
+              fread(&end, 8, 1, f) == 1 && end == kTrsEnd;
+    fclose(f);
+    if (ok) {  // shapes the rest of the library indexes without looking
+        const size_t n = ts->key.size();
+        ok = (int64_t)n == h.n && ts->patlen.size() == n && ts->prof_off.size() == 2 * n + 1 &&
+             ts->cons_off.size() == 2 * n + 1 && ts->fl_off.size() == 4 * n + 1 && ts->leftlen.size() == 2 * n &&
+             ts->rightlen.size() == 2 * n && ts->prof_off.front() == 0 && ts->prof_off.back() == (int64_t)ts->ids.size() &&
+             ts->cons_off.back() == (int64_t)ts->cons.size() && ts->fl_off.back() == (int64_t)ts->fl.size();
+        for (size_t i = 0; ok && i + 1 < ts->prof_off.size(); ++i) ok = ts->prof_off[i] <= ts->prof_off[i + 1];
+        for (size_t i = 0; ok && i + 1 < ts->cons_off.size(); ++i) ok = ts->cons_off[i] <= ts->cons_off[i + 1];
+        for (size_t i = 0; ok && i + 1 < ts->fl_off.size(); ++i) ok = ts->fl_off[i] <= ts->fl_off[i + 1];
+        for (size_t i = 0; ok && i < ts->ids.size(); ++i) ok = ts->ids[i] <= 1000;
+    }
+    if (!ok) {
+        delete ts;
+        return nullptr;
+    }
+    ts->is_read = want.is_read != 0;
+    init_rot(*ts);
+    return ts;
+}
+
+extern "C" int vsk_trset_load_leb36_cached(const char *path, int is_read, int maxflank, int option_r, int reflen,
+                                           const char *cache_path, vsk_trset **out, int *from_cache) {
+    if (from_cache) *from_cache = 0;
+    if (!path || !out) return VSK_ERR_ARG;
+    if (!cache_path || !*cache_path) return vsk_trset_load_leb36(path, is_read, maxflank, option_r, reflen, out);
+    TrsHeader h;
+    memset(&h, 0, sizeof h);
+    memcpy(h.magic, kTrsMagic, 8);
+    h.is_read = is_read != 0;
+    h.maxflank = maxflank;
+    h.option_r = option_r != 0;
+    h.reflen = reflen;
+    if (!source_fingerprint(path, h)) return VSK_ERR_ARG;
+    // n is part of the header that must match: read it from the candidate file itself
+    {
+        TrsHeader got;
+        FILE *f = fopen(cache_path, "rb");
+        if (f) {
+            if (fread(&got, sizeof got, 1, f) == 1) h.n = got.n;
+            fclose(f);
+        }
+    }
+    if (vsk_trset *ts = trset_load_packed(h, cache_path)) {
+        *out = ts;
+        if (from_cache) *from_cache = 1;
+        return VSK_OK;
+    }
+    const int rc = vsk_trset_load_leb36(path, is_read, maxflank, option_r, reflen, out);
+    if (rc != VSK_OK) return rc;
+    h.n = (*out)->n;
+    trset_save_packed(**out, h, cache_path);  // a failure to write is not an error
+    return VSK_OK;
 }
