@@ -47,6 +47,7 @@ class Oracle:
         L.vo_flank_maxerr.argtypes = [C.c_int]
         L.vo_nbdist.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int]
         L.vo_band.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
+        L.vo_cyclic.argtypes = [_i32p, C.c_int, _i32p, C.c_int, _i32p]
         _i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
         _u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
         L.vo_dp_batch.argtypes = [_u16p, _i64p, _u16p, _i64p, _i32p, _i32p, _u8p, C.c_int64, C.c_int, _i32p]
@@ -101,6 +102,14 @@ class Oracle:
         assert rc == 0
         return tuple(int(x) for x in out)
 
+    def cyclic(self, left, top):
+        """GetBestProfileAP restated: (distance, dsum, sumw, length, start rotation)"""
+        left = np.ascontiguousarray(left, dtype=np.int32)
+        top = np.ascontiguousarray(top, dtype=np.int32)
+        out = np.zeros(5, np.int32)
+        assert self.L.vo_cyclic(left, len(left), top, len(top), out) == 0
+        return tuple(int(x) for x in out)
+
     def similarity(self, dsum, sumw):
         return self.L.vo_similarity(dsum, sumw)
 
@@ -142,6 +151,9 @@ class Reference:
         for f in (L.ref_lcs, L.ref_ed_psearch, L.ref_ed_flankalign):
             f.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int]
         L.ref_nbdist.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int]
+        if hasattr(L, "ref_cyclic"):
+            L.ref_cyclic.restype = C.c_double
+            L.ref_cyclic.argtypes = [_i32p, C.c_int, _i32p, C.c_int, _i32p]
         if hasattr(L, "ref_dp_batch"):
             _i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
             _u16p = np.ctypeslib.ndpointer(np.uint16, flags="C_CONTIGUOUS")
@@ -156,6 +168,14 @@ class Reference:
         top = np.ascontiguousarray(top, dtype=np.int32)
         out = np.zeros(4, np.int32)
         sim = self.L.ref_dp(left, len(left), top, len(top), mode, homology, out)
+        return tuple(int(x) for x in out), sim
+
+    def cyclic(self, left, top):
+        """the unmodified GetBestProfileAP: ((distance, dsum, sumw, length, start), similarity)"""
+        left = np.ascontiguousarray(left, dtype=np.int32)
+        top = np.ascontiguousarray(top, dtype=np.int32)
+        out = np.zeros(5, np.int32)
+        sim = self.L.ref_cyclic(left, len(left), top, len(top), out)
         return tuple(int(x) for x in out), sim
 
     def dp_batch(self, loff, lids, toff, tids, li, ti, mode, homology=88):

@@ -140,3 +140,27 @@ void ref_dp_batch( const unsigned short *lids, const long long *loff, const unsi
         free( a );
     }
 }
+
+/* GetBestProfileAP (profile.h:1586-1675): the cyclic aligner (no caller in the reference's programs).
+ * left = p1 (slength rows), top = p2 (plength columns, every rotation of it is tried);
+ * out = {distance, distanceweighted, weights, length, start}; returns similarity */
+double ref_cyclic( const int *left, int l1, const int *top, int l2, int *out ) {
+    PROFILE p1, p2;
+    PAP *   ap;
+    double  sim;
+    memset( &p1, 0, sizeof p1 );
+    memset( &p2, 0, sizeof p2 );
+    p1.proflen = l1;
+    p1.indices = (int *) left;
+    p2.proflen = l2;
+    p2.indices = (int *) top;
+    ap         = GetBestProfileAP( &p1, &p2, g_sm );
+    out[0]     = ap->distance;
+    out[1]     = ap->distanceweighted;
+    out[2]     = ap->weights;
+    out[3]     = ap->length;
+    out[4]     = ap->start;
+    sim        = ap->similarity;
+    FreePAP( ap );
+    return sim;
+}

@@ -540,3 +540,195 @@ void vo_nbdist_batch( const char *a, const int64_t *aoff, const char *b, const i
     vo_strb q = { a, b, aoff, boff, NULL, NULL, NULL, NULL, maxerr, out };
     vo_parallel_for( n, 256, vo_nb_one, &q );
 }
+
+/* ---- cyclic alignment: GetBestProfileAP (profile.h:1586-1675) -------------------------------
+ * Dead code in the reference's programs, but it is the aligner VNTRseek's description means by
+ * "rotation-aware": the left profile (l1 rows) is aligned globally against every rotation of the
+ * top profile (l2 columns), i.e. against the windows [m, m+l2] of the doubled top profile, and the
+ * rotation with the smallest weighted distance per weight wins (strict <, in the order the
+ * reference visits them: m = 0 first, then midpoints depth-first, left half before right half).
+ * Rotation m is aligned only between the paths found for the rotations `lo` < m < `hi` that
+ * enclose it (GetBoundedProfileAP, profile.h:1281-1585): row r may use columns
+ * max(left-most column of lo's path in row r, m) .. min(right-most column of hi's path, m+l2);
+ * the cell left of a cut-off row and the cells right of a row's end up to the next row's end are
+ * PA_VLN.  Recurrence and tie-break as vo_dp; the weighted sums come from the traceback.
+ * out = {distance, distanceweighted, weights, length, start}.  Returns 0, or -1 on bad input.   */
+#define VO_VLN 600000000
+typedef struct {
+    int left, right;
+} vo_lim;
+
+typedef struct {
+    int distance, dsum, sumw, length;
+} vo_pap;
+
+/* one bounded alignment; writes the limits of its own path to `own` (PAPToLimit, profile.h:1231-1279) */
+static vo_pap vo_bounded( const int32_t *left, const int32_t *top2, int l1, int start, int end,
+  const vo_lim *mins, const vo_lim *maxs, int *D, uint8_t *dir, vo_lim *own ) {
+    const int width = end - start + 1;
+    int       r, c, i, max, min;
+    vo_pap    ap;
+#define DD( r, c ) D[(size_t) ( r ) * width + ( ( c ) - start )]
+#define RR( r, c ) dir[(size_t) ( r ) * width + ( ( c ) - start )]
+    DD( 0, start ) = 0;
+    RR( 0, start ) = 0;
+    max            = maxs[0].right < end ? maxs[0].right : end;
+    for ( c = start + 1; c <= max; c++ ) {
+        DD( 0, c ) = vo_dist[0][top2[c - 1]] + DD( 0, c - 1 );
+        RR( 0, c ) = 3;
+    }
+    {
+        int nxt = maxs[1].right < end ? maxs[1].right : end;
+        for ( i = nxt; i > max; i-- )
+            DD( 0, i ) = VO_VLN;
+    }
+    for ( r = 1; r <= l1; r++ ) { /* start column, while the left bound does not cut it off */
+        DD( r, start ) = vo_dist[0][left[r - 1]] + DD( r - 1, start );
+        RR( r, start ) = 2;
+        if ( r < l1 ) {
+            min = mins[r + 1].left > start ? mins[r + 1].left : start;
+            if ( min > start )
+                break;
+        }
+    }
+    for ( r = 1; r <= l1; r++ ) {
+        const int l = left[r - 1], gl = vo_dist[0][l];
+        min = mins[r].left > start ? mins[r].left : start;
+        max = maxs[r].right < end ? maxs[r].right : end;
+        if ( min > start ) {
+            DD( r, min - 1 ) = VO_VLN;
+            c                = min;
+        } else {
+            c = min + 1;
+        }
+        for ( ; c <= max; c++ ) {
+            const int t = top2[c - 1];
+            const int e = DD( r, c - 1 ) + vo_dist[0][t], f = DD( r - 1, c ) + gl, sa = DD( r - 1, c - 1 ) + vo_dist[l][t];
+            if ( sa <= f && sa <= e ) {
+                DD( r, c ) = sa;
+                RR( r, c ) = 1;
+            } else if ( f <= e ) {
+                DD( r, c ) = f;
+                RR( r, c ) = 2;
+            } else {
+                DD( r, c ) = e;
+                RR( r, c ) = 3;
+            }
+        }
+        if ( r < l1 ) {
+            int nxt = maxs[r + 1].right < end ? maxs[r + 1].right : end;
+            for ( i = nxt; i > max; i-- )
+                DD( r, i ) = VO_VLN;
+        }
+    }
+    /* traceback: length, weighted sums (profile.h:1429-1497), and the path's limits */
+    ap.distance = DD( l1, end );
+    ap.length = ap.dsum = ap.sumw = 0;
+    r = l1;
+    c = end;
+    for ( i = 0; i <= l1; i++ ) {
+        own[i].left  = 0x7fffffff;
+        own[i].right = -1;
+    }
+    for ( ;; ) {
+        const int d = RR( r, c );
+        if ( c < own[r].left )
+            own[r].left = c;
+        if ( c > own[r].right )
+            own[r].right = c;
+        if ( d == 1 ) {
+            const int l = left[r - 1], t = top2[c - 1];
+            int       dn = vo_nd[l] + vo_nd[t];
+            if ( dn > 10 )
+                dn = 10;
+            ap.dsum += dn * vo_dist[l][t];
+            ap.sumw += dn;
+            r--;
+            c--;
+        } else if ( d == 3 ) {
+            const int t = top2[c - 1];
+            ap.dsum += vo_nd[t] * vo_dist[0][t];
+            ap.sumw += vo_nd[t];
+            c--;
+        } else if ( d == 2 ) {
+            const int l = left[r - 1];
+            ap.dsum += vo_nd[l] * vo_dist[l][0];
+            ap.sumw += vo_nd[l];
+            r--;
+        } else
+            break;
+        ap.length++;
+    }
+#undef DD
+#undef RR
+    return ap;
+}
+
+int vo_cyclic( const int32_t *left, int l1, const int32_t *top, int l2, int32_t *out ) {
+    int32_t *top2;
+    int *    D;
+    uint8_t *dir;
+    vo_lim **lim; /* limits of the rotations on the current path of the recursion, by rotation */
+    int      stackl[64], stackr[64], sp = -1, m, i, best_start = 0;
+    vo_pap   best, ap;
+    if ( !vo_ready || l1 < 1 || l2 < 1 )
+        return -1;
+    top2 = (int32_t *) malloc( sizeof( int32_t ) * 2 * l2 );
+    for ( i = 0; i < 2 * l2; i++ )
+        top2[i] = top[i % l2];
+    D   = (int *) malloc( sizeof( int ) * (size_t) ( l1 + 1 ) * ( l2 + 1 ) );
+    dir = (uint8_t *) malloc( (size_t) ( l1 + 1 ) * ( l2 + 1 ) );
+    lim = (vo_lim **) calloc( (size_t) l2 + 1, sizeof( vo_lim * ) );
+    lim[0]  = (vo_lim *) malloc( sizeof( vo_lim ) * ( l1 + 2 ) );
+    lim[l2] = (vo_lim *) malloc( sizeof( vo_lim ) * ( l1 + 2 ) );
+    for ( i = 0; i <= l1 + 1; i++ ) { /* init_rectangular_limits, profile.h:1219-1229 */
+        lim[0][i].left = lim[0][i].right = 0;
+        lim[l2][i].left = lim[l2][i].right = l2;
+    }
+    {
+        vo_lim *own = (vo_lim *) malloc( sizeof( vo_lim ) * ( l1 + 2 ) );
+        best        = vo_bounded( left, top2, l1, 0, l2, lim[0], lim[l2], D, dir, own );
+        own[l1 + 1] = own[l1];
+        free( lim[0] );
+        lim[0] = own;
+        for ( i = 0; i <= l1 + 1; i++ ) { /* the same path, one period to the right */
+            lim[l2][i].left  = lim[0][i].left + l2;
+            lim[l2][i].right = lim[0][i].right + l2;
+        }
+    }
+    stackl[++sp] = 0;
+    stackr[sp]   = l2;
+    while ( sp >= 0 ) {
+        const int lo = stackl[sp], hi = stackr[sp];
+        sp--;
+        if ( hi - lo > 1 ) {
+            vo_lim *own = (vo_lim *) malloc( sizeof( vo_lim ) * ( l1 + 2 ) );
+            m           = ( lo + hi ) / 2;
+            ap          = vo_bounded( left, top2, l1, m, m + l2, lim[lo], lim[hi], D, dir, own );
+            own[l1 + 1] = own[l1];
+            lim[m]      = own;
+            if ( ( ap.dsum / ( 255.0 * ap.sumw ) ) < ( best.dsum / ( 255.0 * best.sumw ) ) ) {
+                best       = ap;
+                best_start = m;
+            }
+            stackl[++sp] = m; /* the left half is popped first */
+            stackr[sp]   = hi;
+            stackl[++sp] = lo;
+            stackr[sp]   = m;
+        } else { /* removelimits(left), profile.h:1649 */
+            free( lim[lo] );
+            lim[lo] = NULL;
+        }
+    }
+    free( lim[l2] );
+    free( lim );
+    free( D );
+    free( dir );
+    free( top2 );
+    out[0] = best.distance;
+    out[1] = best.dsum;
+    out[2] = best.sumw;
+    out[3] = best.length;
+    out[4] = best_start;
+    return 0;
+}

@@ -17,7 +17,7 @@ j = np.fromfile("/tmp/jobs.bin", dtype=np.int32).reshape(-1, 3)
 l1, l2, br = j[:, 0].astype(np.int64), j[:, 1].astype(np.int64), j[:, 2]
 cells = l1 * l2
 print("pairs", len(j), "cells", cells.sum(), "banded frac", (br >= 0).mean())
-edges = [0, 16, 32, 64, 128, 256, 512, 1024, 2048, 8192]
+edges = [0, 32, 64, 128, 192, 256, 384, 512, 768, 1024, 1536, 2048, 8192]
 for a, b in zip(edges[:-1], edges[1:]):
     m = (l2 > a) & (l2 <= b)
     print(f"l2 in ({a},{b}]: pairs {m.mean()*100:6.2f}%  cells {cells[m].sum()/cells.sum()*100:6.2f}%  mean l1 {l1[m].mean() if m.any() else 0:.0f}")

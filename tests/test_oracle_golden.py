@@ -69,3 +69,28 @@ def test_oracle_vs_reference_live(oracle, reference):
         top = rng.integers(0, 1001, l2)
         for m in (0, 1):
             assert oracle.dp(left, top, m) == reference.dp(left, top, m)[0]
+
+
+def test_cyclic_golden(oracle):
+    """the cyclic aligner's restatement (vo_cyclic) against known answers recorded from the unmodified
+    GetBestProfileAP (tests/golden/make_cyclic_golden.py): distance, weighted sums, length, rotation"""
+    g = golden("kat_cyclic.npz")
+    profs = _profiles(g)
+    for k, (exp, sim) in enumerate(zip(g["expect"], g["similarity"])):
+        got = oracle.cyclic(profs[2 * k], profs[2 * k + 1])
+        assert got == tuple(int(x) for x in exp), (k, len(profs[2 * k]), len(profs[2 * k + 1]))
+        if exp[2] != 0:
+            assert oracle.similarity(got[1], got[2]) == sim
+    assert (g["expect"][:, 4] != 0).sum() > 100
+
+
+def test_cyclic_vs_reference_live(oracle, reference):
+    from vntrseek_b200 import synth
+    rng = np.random.default_rng(77)
+    for k in range(150):
+        L = int(rng.integers(1, 150))
+        a = synth._column_ids(rng, rng.integers(0, 4, L)).astype(np.int32)
+        b = np.roll(synth._mutate_profile(rng, a, 0.08, 0.04), int(rng.integers(0, L))) if (k % 2 and L >= 7) else \
+            rng.integers(0, 1001, int(rng.integers(1, 200)))
+        b = np.asarray(b, np.int32)
+        assert oracle.cyclic(a, b) == reference.cyclic(a, b)[0], (k, len(a), len(b))
