@@ -98,6 +98,21 @@ int vsk_dp_batch_fetch(vsk_ctx *ctx, vsk_dp_batch *b, vsk_dp_result *out);
 int64_t vsk_dp_batch_cells(const vsk_dp_batch *b);
 void vsk_dp_batch_free(vsk_ctx *ctx, vsk_dp_batch *b);
 
+/* ---- cyclic pair DP -----------------------------------------------------------------
+ * GetBestProfileAP (profile.h:1586-1675, with GetBoundedProfileAP :1281-1585 and PAPToLimit
+ * :1231-1279): the left profile against EVERY rotation of the top profile, each rotation aligned
+ * between the paths of the rotations that enclose it, best weighted distance wins (ties: the
+ * rotation the reference visits first).  No program of the reference calls this aligner; it is
+ * offered for rotation-invariant matching and is not part of vsk_proclu_run.  Profiles of
+ * 1..VSK_CYCLIC_MAX columns.  out[i].start = the winning rotation (PAP.start).               */
+#define VSK_CYCLIC_MAX 1024
+typedef struct {
+    int32_t distance, dsum, sumw, length, start;
+    int32_t pad_[3];
+} vsk_cyclic_result;
+int vsk_pair_dp_cyclic(vsk_ctx *ctx, const vsk_profset *left_set, const vsk_profset *top_set, int64_t n,
+                       const int32_t *left_idx, const int32_t *top_idx, vsk_cyclic_result *out);
+
 /* ---- pair DP without any allocation ------------------------------------------------
  * (No counterpart in the reference: it exists for hosts of this library that cannot
  * allocate device memory when they need an alignment -- the GPU is owned by the

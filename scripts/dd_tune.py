@@ -44,7 +44,7 @@ print()
 ''' % (ROOT, os.path.join(ROOT, "tests", "golden", "dist_table.npz"))
 
 sizes = sys.argv[1:] or ["134", "201", "303", "474", "715", "1111", "1500", "2000"]
-for force in [""] + (os.environ.get("DD_TUNE_FORCES", "qp16 qp12 qp8 t16 t12 t8").split()):
+for force in [""] + (os.environ.get("DD_TUNE_FORCES", "16 12 8").split()):
     env = dict(os.environ)
     if force:
         env["VSK_DD_FORCE"] = force

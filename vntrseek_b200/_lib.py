@@ -46,6 +46,7 @@ def _declare(L):
     L.vsk_profset_free.restype = None
     L.vsk_pair_dp.argtypes = [vp, vp, vp, C.c_int64, _p(np.int32), _p(np.int32), _p(np.uint8),
                               C.c_int, _p(np.int32)]
+    L.vsk_pair_dp_cyclic.argtypes = [vp, vp, vp, C.c_int64, _p(np.int32), _p(np.int32), _p(np.int32)]
     L.vsk_dp_batch_prepare.argtypes = [vp, vp, vp, C.c_int64, _p(np.int32), _p(np.int32),
                                        _p(np.uint8), C.c_int, C.POINTER(vp)]
     L.vsk_dp_batch_run.argtypes = [vp, vp]

@@ -150,6 +150,14 @@ class Context:
         self._check(lib().vsk_pair_dp(self.h, left.h, top.h, len(li), li, ti, mode, homology, out))
         return out[:len(li)]
 
+    def pair_dp_cyclic(self, left, top, li, ti):
+        """vsk_pair_dp_cyclic (GetBestProfileAP): rows of (distance, dsum, sumw, length, start rotation)"""
+        li = np.ascontiguousarray(li, np.int32)
+        ti = np.ascontiguousarray(ti, np.int32)
+        out = np.zeros((max(len(li), 1), 8), np.int32)
+        self._check(lib().vsk_pair_dp_cyclic(self.h, left.h, top.h, len(li), li, ti, out))
+        return out[:len(li), :5]
+
     def dp_batch(self, left, top, li, ti, mode, homology=88):
         return DpBatch(self, left, top, li, ti, mode, homology)
 

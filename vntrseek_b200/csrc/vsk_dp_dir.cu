@@ -21,27 +21,20 @@
 // eighth step all lanes store their last complete group of 8 rows as one sector.
 #include <algorithm>
 #include <cstdlib>
-#include <type_traits>
 
 #include <cub/cub.cuh>
 
 #include "vsk_internal.cuh"
 
 #define DD_WARPS 4
-#define DD_TBYTES 8192   // per warp: compact table [na][nb], or the query profile of a strip [row symbol][lane][CPL]
+#define DD_TBYTES 8192
 #define DD_MAXCPL 16
-#define DD_MAXNA 32      // row alphabets up to this size can have a query profile (at 8 columns per lane)
 #define DD_FULL 0xffffffffu
-// how the sweep finds d(row symbol, column symbol)
-#define DD_GLOBAL 0  // one byte load per cell from the symmetric table in global memory
-#define DD_SMEMT 1   // one byte load per cell from the pair's compact table in shared memory
-#define DD_QP 2      // one vector load per row from the strip's query profile, bytes picked by dp4a
 
 struct DdWarpSmem {
-    uint8_t T[DD_TBYTES];   // query profile of the current strip, or compact substitution table [na][nb]
+    uint8_t T[DD_TBYTES];   // compact substitution table [na][nb]
     uint32_t bmL[32], bmT[32];
     uint16_t preT[32];
-    uint16_t rowid[DD_MAXNA + 32];  // local row symbol -> composition id (query profile is rebuilt per strip)
     uint32_t win[64];       // sliding window of row records, slot = row & 63 (steady phase)
     union {
         struct {                 // while the pair is set up
@@ -53,42 +46,35 @@ struct DdWarpSmem {
 };
 #define DD_SMEM_BYTES (2048 + DD_WARPS * sizeof(DdWarpSmem))
 
-// Columns per lane (8, 12 or 16), number of column strips and table mode of a pair with l2 columns whose
-// reference-side profile uses `na` distinct compositions.  A query profile holds, for every row symbol,
-// the costs against the strip's 32*cpl columns laid out so that a lane finds its cpl bytes in one vector
-// load: na * 32 * cpl bytes, which bounds cpl by na.  Cost model in issued instructions: per strip and
-// wavefront step a fixed part plus cpl cells (fewer instructions per cell with a query profile).
-__host__ __device__ inline void dd_plan(int l2, int na, int &cpl, int &ns, bool &qp) {
+// Columns per lane and number of column strips of a pair: the cheapest of 8, 12, 16 columns per lane, in
+// issued instructions per wavefront step (11 per cell + about 50 that do not depend on the strip width).
+// `force` (tuning aid, VSK_DD_FORCE=8|12|16) overrides the choice.
+__host__ __device__ inline void dd_plan(int l2, int force, int &cpl, int &ns) {
     int best = 0x7fffffff;
     cpl = 16;
     ns = 1;
-    qp = false;
 #pragma unroll
-    for (int m = 1; m >= 0; --m)
-#pragma unroll
-        for (int c = 16; c >= 8; c -= 4) {
-            if (m == 1 && (na > DD_MAXNA || na * 32 * c > DD_TBYTES)) continue;
-            const int n = (l2 + 32 * c - 1) / (32 * c);
-            const int cost = n * (m ? (c * 8 + 40) : (c * 11 + 50));
-            if (cost < best) {
-                best = cost;
-                cpl = c;
-                ns = n;
-                qp = (m == 1);
-            }
+    for (int c = 16; c >= 8; c -= 4) {
+        const int n = (l2 + 32 * c - 1) / (32 * c);
+        const int cost = n * (c * 11 + 50);  // x (l1 + 31) steps either way
+        if (force ? (c == force) : (cost < best)) {
+            best = cost;
+            cpl = c;
+            ns = n;
         }
+    }
 }
 
-// row record: bits 0..15 table row offset (query profile: local index * 32*cpl; compact table: local index *
-// nb; global table: the id), 16..23 gap cost d(0,l)
+// row record: bits 0..15 table row offset (local index * nb, or the id for the global table),
+// 16..23 gap cost d(0,l)
 __device__ __forceinline__ uint32_t dd_pack_row(int off, int gn) {
     return (uint32_t)off | ((uint32_t)(gn & 255) << 16);
 }
 
-// local alphabets, table mode, compact table, row records; returns the mode, nb and na
-__device__ __forceinline__ int dd_setup(const uint16_t *__restrict__ L, const uint16_t *__restrict__ Tp, int l1, int l2,
-                                        const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
-                                        uint32_t *rowrec, bool want_qp, int cpl, int &nb_out, int &na_out) {
+// local alphabets, compact table, row records (same scheme as vsk_dp_kernel); returns nb, smemt
+__device__ __forceinline__ bool dd_setup(const uint16_t *__restrict__ L, const uint16_t *__restrict__ Tp, int l1, int l2,
+                                         const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
+                                         uint32_t *rowrec, int &nb_out) {
     const int lane = threadIdx.x & 31;
     ws.bmL[lane] = 0;
     ws.bmT[lane] = 0;
@@ -112,10 +98,8 @@ __device__ __forceinline__ int dd_setup(const uint16_t *__restrict__ L, const ui
         if (lane >= o) { xl += a; xt += b; }
     }
     const int na = __shfl_sync(DD_FULL, xl, 31), nb = __shfl_sync(DD_FULL, xt, 31);
-    int mode = DD_GLOBAL;
-    if (want_qp && na <= DD_MAXNA && na * 32 * cpl <= DD_TBYTES) mode = DD_QP;
-    else if ((na <= 256) && (nb <= 256) && (na * nb <= DD_TBYTES)) mode = DD_SMEMT;
-    if (mode != DD_GLOBAL) {
+    const bool smemt = (na <= 256) && (nb <= 256) && (na * nb <= DD_TBYTES);
+    if (smemt) {
         ws.preT[lane] = (uint16_t)(xt - ct);
         uint32_t b = bl;
         int rk = xl - cl;
@@ -124,11 +108,10 @@ __device__ __forceinline__ int dd_setup(const uint16_t *__restrict__ L, const ui
             b &= b - 1;
             ws.u.su.mapL[id] = (uint8_t)rk;
             ws.u.su.invL[rk] = (uint16_t)id;
-            if (mode == DD_QP) ws.rowid[rk] = (uint16_t)id;
             ++rk;
         }
-        b = (mode == DD_SMEMT) ? bt : 0u;  // column symbols by rank: the compact table only (nb <= 256 there;
-        rk = xt - ct;                       // a query profile is indexed by column position, whatever nb is)
+        b = bt;
+        rk = xt - ct;
         while (b) {
             const int id = lane * 32 + __ffs(b) - 1;
             b &= b - 1;
@@ -136,39 +119,34 @@ __device__ __forceinline__ int dd_setup(const uint16_t *__restrict__ L, const ui
             ++rk;
         }
         __syncwarp();
-        if (mode == DD_SMEMT) {
 #pragma unroll 4
-            for (int a = 0; a < na; ++a) {
-                const uint8_t *drow = dist + (int)ws.u.su.invL[a] * VSK_DROW;
-                for (int c = lane; c < nb; c += 32) ws.T[a * nb + c] = __ldg(drow + ws.u.su.invT[c]);
-            }
+        for (int a = 0; a < na; ++a) {
+            const uint8_t *drow = dist + (int)ws.u.su.invL[a] * VSK_DROW;
+            for (int c = lane; c < nb; c += 32) ws.T[a * nb + c] = __ldg(drow + ws.u.su.invT[c]);
         }
         __syncwarp();
     }
-    const int rstride = (mode == DD_QP) ? 32 * cpl : nb;
     for (int i = lane; i < l1; i += 32) {
         const int id = L[i];
-        rowrec[i] = dd_pack_row(mode != DD_GLOBAL ? (int)ws.u.su.mapL[id] * rstride : id, s_gapnd[id]);
+        rowrec[i] = dd_pack_row(smemt ? (int)ws.u.su.mapL[id] * nb : id, s_gapnd[id]);
     }
     __syncwarp();
     nb_out = nb;
-    na_out = na;
-    return mode;
+    return smemt;
 }
 
 // One row of a lane's CPL cells.  Hin = the previous row of these columns, Hout = this row (the two may be
-// the same array).  q[] = the lane's bytes of the query profile row (MODE == DD_QP).
-template <int CPL, int MODE>
+// the same array).
+template <int CPL, bool SMEMT>
 __device__ __forceinline__ uint32_t dd_row_cells(const int (&Hin)[CPL], int (&Hout)[CPL], const int (&tb)[CPL],
-                                                 const int (&gt)[CPL], const uint32_t (&q)[CPL / 4], int dgd, int lfd,
+                                                 const int (&gt)[CPL], int dgd, int lfd,
                                                  const uint8_t *__restrict__ trow, int gl) {
     uint32_t w = 0;
 #pragma unroll
     for (int j = 0; j < CPL; ++j) {
         const int upd = Hin[j];
-        int sa;  // diagonal
-        if (MODE == DD_QP) sa = (int)__dp4a(q[j >> 2], 1u << (8 * (j & 3)), (unsigned)dgd);
-        else sa = dgd + (MODE == DD_SMEMT ? (int)trow[tb[j]] : (int)__ldg(trow + tb[j]));
+        const int dlt = SMEMT ? (int)trow[tb[j]] : (int)__ldg(trow + tb[j]);
+        const int sa = dgd + dlt;   // diagonal
         const int f = upd + gl;     // down
         const int e = lfd + gt[j];  // right
         // min3switch (profile.h:1098-1099): diag if sa<=f && sa<=e; else down if f<=e; else right.
@@ -192,25 +170,10 @@ __device__ __forceinline__ void dd_flush8(const DdWarpSmem &ws, int lane, uint32
     __stcs(dst + 1, b);
 }
 
-// the lane's CPL bytes of a query profile row
-template <int CPL>
-__device__ __forceinline__ void dd_load_q(const uint8_t *p, uint32_t (&q)[CPL / 4]) {
-    if (CPL == 16) {
-        const uint4 v = *reinterpret_cast<const uint4 *>(p);
-        q[0] = v.x; q[1] = v.y; q[2] = v.z; q[CPL / 4 - 1] = v.w;
-    } else if (CPL == 8) {
-        const uint2 v = *reinterpret_cast<const uint2 *>(p);
-        q[0] = v.x; q[CPL / 4 - 1] = v.y;
-    } else {
-#pragma unroll
-        for (int k = 0; k < CPL / 4; ++k) q[k] = reinterpret_cast<const uint32_t *>(p)[k];
-    }
-}
-
-template <int CPL, int MODE>
+template <int CPL, bool SMEMT>
 __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *__restrict__ Tp,
                                         const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
-                                        int na, int *bscr, const uint32_t *rowrec, uint32_t *__restrict__ dir,
+                                        int nb, int *bscr, const uint32_t *rowrec, uint32_t *__restrict__ dir,
                                         int4 *out) {
     const int lane = threadIdx.x & 31;
     const int l1 = job.l1, l2 = job.l2, br = job.br;
@@ -220,7 +183,6 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
     int totd = 0;
     int Hd[CPL];
     int prev_r_hi = l1;
-    const uint8_t *qlane = ws.T + lane * CPL;  // this lane's bytes inside a query profile row
 
     for (int pass = 0; pass < npass; ++pass) {
         const int cbase = pass * (32 * CPL) + lane * CPL;
@@ -232,7 +194,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             const int id = (c < l2) ? (int)Tp[c] : 0;
             const int g = s_gapnd[id] & 255;
             gt[j] = g;
-            if (MODE == DD_SMEMT) {
+            if (SMEMT) {
                 const int w = id >> 5;
                 tb[j] = ws.preT[w] + __popc(ws.bmT[w] & ((1u << (id & 31)) - 1u));
             } else {
@@ -240,22 +202,6 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             }
             sd += g;
             Hd[j] = sd;
-        }
-        if (MODE == DD_QP) {
-            // query profile of this strip: row symbol a, this lane's columns -> CPL bytes at a*32*CPL + lane*CPL
-            // (the previous strip's sweep is over: every lane passed the __syncwarp at the end of the loop body)
-            for (int a = 0; a < na; ++a) {
-                const uint8_t *drow = dist + (int)ws.rowid[a] * VSK_DROW;
-                uint32_t wds[CPL / 4];
-#pragma unroll
-                for (int k = 0; k < CPL / 4; ++k) wds[k] = 0;
-#pragma unroll
-                for (int j = 0; j < CPL; ++j) wds[j >> 2] |= (uint32_t)__ldg(drow + tb[j]) << (8 * (j & 3));
-                uint32_t *dstw = reinterpret_cast<uint32_t *>(ws.T + a * (32 * CPL) + lane * CPL);
-#pragma unroll
-                for (int k = 0; k < CPL / 4; ++k) dstw[k] = wds[k];
-            }
-            __syncwarp();
         }
         int xd = sd;
 #pragma unroll
@@ -287,35 +233,34 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             for (int j = 0; j < CPL; ++j) Hd[j] = VSK_BIG;
             dgd = VSK_BIG;
         }
-        const bool rd_scratch = (lane == 0) && (pass > 0);
+        const bool first = (pass == 0);
         const bool wr_scratch = (lane == 31) && (pass < npass - 1);
         int nxt = VSK_BIG;
-        if (rd_scratch && r_lo < prev_r_hi) nxt = __ldcg(bscr + r_lo);
+        if (lane == 0 && !first && r_lo < prev_r_hi) nxt = __ldcg(bscr + r_lo);
         uint32_t rec_next = __ldcg(rowrec + min(max(r_lo - lane, 0), l1 - 1));
         const int l1p = (l1 + 7) & ~7;
         uint32_t *dlane = dir + (size_t)(pass * 32 + lane) * l1p;  // this lane's words, row-indexed
         const int g_lo = r_lo & ~7;
 
-        auto step = [&](const int s, const bool check) {
+        // a step with range checks: pipeline fill and drain (lanes whose row is outside [r_lo, r_hi) idle)
+        auto step = [&](const int s) {
             const int r = s - lane;
             int lfd = __shfl_up_sync(DD_FULL, Hd[CPL - 1], 1);
-            const bool active = !check || ((r >= r_lo) && (r < r_hi));
+            const bool active = (r >= r_lo) && (r < r_hi);
             const uint32_t rec = rec_next;
             rec_next = __ldcg(rowrec + min(max(r + 1, 0), l1 - 1));
             const int gl = (int)(rec >> 16);
-            const uint8_t *trow = (MODE == DD_SMEMT) ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
+            const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
             if (active) {
                 if (lane == 0) {
-                    if (pass == 0) {
+                    if (first) {
                         lfd = dgd + gl;  // column 0, profile.h:2084-2090
                     } else {
                         lfd = nxt;
                         nxt = (r + 1 < prev_r_hi) ? __ldcg(bscr + r + 1) : VSK_BIG;
                     }
                 }
-                uint32_t q[CPL / 4];
-                if (MODE == DD_QP) dd_load_q<CPL>(qlane + (rec & 0xffffu), q);
-                const uint32_t w = dd_row_cells<CPL, MODE>(Hd, Hd, tb, gt, q, dgd, lfd, trow, gl);
+                const uint32_t w = dd_row_cells<CPL, SMEMT>(Hd, Hd, tb, gt, dgd, lfd, trow, gl);
                 dgd = lfd;
                 ws.u.ring[lane][r & 15] = w;
                 if (wr_scratch) bscr[r] = Hd[CPL - 1];
@@ -325,91 +270,74 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                 if (g0 >= g_lo) dd_flush8(ws, lane, dlane, g0);
             }
         };
+        // Steps r_lo .. r_hi+30.  The middle ones, where every lane has a row, run in the steady loop below,
+        // two rows per trip (so their number is made even: an odd one out is taken by the checked step).
         const int s_fill_end = min(r_lo + 31, r_hi + 31);
+        const int n_steady = max(0, r_hi - s_fill_end);
+        const int s_steady_begin = s_fill_end + (n_steady & 1);
         int s = r_lo;
-        for (; s < s_fill_end; ++s) step(s, true);
-        if (s < r_hi) {
-            // steady phase: every lane has a row in [r_lo, r_hi) and every step sends a row out; the
-            // addresses advance by one row per step (the scratch has a row of slack past l1)
-            int *bp = bscr + (s - lane);                   // lane 31 leaves its row's last cell here
-            // Row records come through a 64-row window in shared memory and the left neighbours of
-            // lane 0 through a register per lane, both fetched a block of 32 steps ahead, so that no
-            // step waits for global memory.
-            __syncwarp();
-            ws.win[(s - 31 + lane) & 63] = __ldcg(rowrec + s - 31 + lane);
-            ws.win[(s + 1 + lane) & 63] = __ldcg(rowrec + s + 1 + lane);
-            int bcur = (pass > 0) ? __ldcg(bscr + s + 1 + lane) : 0, bpre = 0;
-            uint32_t wpre = 0;
-            __syncwarp();
-            rec_next = ws.win[(s - lane) & 63];
-            int k = 0;
-            // one steady step: previous row of the lane's columns in Hin, this row into Hout.  The loop
-            // below runs it twice per trip with the two arrays swapping roles, so no row is copied.
-            auto steady = [&](auto first_c, const int (&Hin)[CPL], int (&Hout)[CPL]) {
-                constexpr bool FIRST = decltype(first_c)::value;  // first strip: column 0 instead of a previous strip
-                const int r = s - lane;
-                if ((k & 31) == 0) {  // rows s+33 .. s+64: needed from step s+32 on
-                    wpre = __ldcg(rowrec + s + 33 + lane);
-                    if (!FIRST) bpre = __ldcg(bscr + s + 33 + lane);
-                }
-                int lfd = __shfl_up_sync(DD_FULL, Hin[CPL - 1], 1);
-                const uint32_t rec = rec_next;
-                rec_next = ws.win[(r + 1) & 63];
-                const int gl = (int)(rec >> 16);
-                const uint8_t *trow = (MODE == DD_SMEMT) ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
-                uint32_t q[CPL / 4];
-                if (MODE == DD_QP) dd_load_q<CPL>(qlane + (rec & 0xffffu), q);
-                if (FIRST) {
-                    if (lane == 0) lfd = dgd + gl;  // column 0, profile.h:2084-2090
-                } else {
+#pragma unroll 1
+        for (int phase = 0; phase < 2; ++phase) {  // one copy of the checked step serves fill and drain
+            const int lim = phase ? r_hi + 31 : s_steady_begin;
+#pragma unroll 1
+            for (; s < lim; ++s) step(s);
+            if (phase == 0 && s < r_hi) {
+                // steady phase: every lane has a row in [r_lo, r_hi) and every step sends a row out; the
+                // addresses advance by one row per step (the scratch has a row of slack past l1)
+                int *bp = bscr + (s - lane);                   // lane 31 leaves its row's last cell here
+                // Row records come through a 64-row window in shared memory and the left neighbours of
+                // lane 0 through a register per lane, both fetched a block of 32 steps ahead, so that no
+                // step waits for global memory.
+                __syncwarp();
+                ws.win[(s - 31 + lane) & 63] = __ldcg(rowrec + s - 31 + lane);
+                ws.win[(s + 1 + lane) & 63] = __ldcg(rowrec + s + 1 + lane);
+                int bcur = first ? 0 : __ldcg(bscr + s + 1 + lane), bpre = 0;
+                uint32_t wpre = 0;
+                __syncwarp();
+                rec_next = ws.win[(s - lane) & 63];
+                int k = 0;
+                // one steady step: previous row of the lane's columns in Hin, this row into Hout.  The loop
+                // runs it twice per trip with the two arrays swapping roles, so no row is copied.
+                auto steady = [&](const int (&Hin)[CPL], int (&Hout)[CPL]) {
+                    const int r = s - lane;
+                    if ((k & 31) == 0) {  // rows s+33 .. s+64: needed from step s+32 on
+                        wpre = __ldcg(rowrec + s + 33 + lane);
+                        if (!first) bpre = __ldcg(bscr + s + 33 + lane);
+                    }
+                    int lfd = __shfl_up_sync(DD_FULL, Hin[CPL - 1], 1);
+                    const uint32_t rec = rec_next;
+                    rec_next = ws.win[(r + 1) & 63];
+                    const int gl = (int)(rec >> 16);
+                    const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
                     const int v = __shfl_sync(DD_FULL, bcur, k & 31);  // previous strip's last cell of row s+1
-                    if (lane == 0) lfd = nxt;
+                    if (lane == 0) lfd = first ? dgd + gl : nxt;       // column 0 (profile.h:2084-2090) : boundary
                     nxt = (s + 1 < prev_r_hi) ? v : VSK_BIG;
-                }
-                const uint32_t w = dd_row_cells<CPL, MODE>(Hin, Hout, tb, gt, q, dgd, lfd, trow, gl);
-                dgd = lfd;
-                ws.u.ring[lane][r & 15] = w;
-                if (wr_scratch) *bp = Hout[CPL - 1];
-                ++bp;
-                if ((s & 7) == 7) {  // the lane's last complete group of 8 rows goes out
-                    const int g0 = ((r + 1) & ~7) - 8;
-                    if (g0 >= g_lo) dd_flush8(ws, lane, dlane, g0);
-                }
-                if ((k & 31) == 31) {  // rows <= s-31 are done with: their slots take rows s+2 .. s+33
-                    __syncwarp();
-                    ws.win[(s + 2 + lane) & 63] = wpre;
-                    bcur = bpre;
-                    __syncwarp();
-                }
-                ++s;
-                ++k;
-            };
-            int Hx[CPL];
-            if (pass == 0) {
-                const std::true_type first;
-                while (s + 1 < r_hi) {
-                    steady(first, Hd, Hx);
-                    steady(first, Hx, Hd);
-                }
-                if (s < r_hi) {
-                    steady(first, Hd, Hx);
-#pragma unroll
-                    for (int j = 0; j < CPL; ++j) Hd[j] = Hx[j];
-                }
-            } else {
-                const std::false_type later;
-                while (s + 1 < r_hi) {
-                    steady(later, Hd, Hx);
-                    steady(later, Hx, Hd);
-                }
-                if (s < r_hi) {
-                    steady(later, Hd, Hx);
-#pragma unroll
-                    for (int j = 0; j < CPL; ++j) Hd[j] = Hx[j];
+                    const uint32_t w = dd_row_cells<CPL, SMEMT>(Hin, Hout, tb, gt, dgd, lfd, trow, gl);
+                    dgd = lfd;
+                    ws.u.ring[lane][r & 15] = w;
+                    if (wr_scratch) *bp = Hout[CPL - 1];
+                    ++bp;
+                    if ((s & 7) == 7) {  // the lane's last complete group of 8 rows goes out
+                        const int g0 = ((r + 1) & ~7) - 8;
+                        if (g0 >= g_lo) dd_flush8(ws, lane, dlane, g0);
+                    }
+                    if ((k & 31) == 31) {  // rows <= s-31 are done with: their slots take rows s+2 .. s+33
+                        __syncwarp();
+                        ws.win[(s + 2 + lane) & 63] = wpre;
+                        bcur = bpre;
+                        __syncwarp();
+                    }
+                    ++s;
+                    ++k;
+                };
+                int Hx[CPL];
+#pragma unroll 1
+                while (s < r_hi) {
+                    steady(Hd, Hx);
+                    steady(Hx, Hd);
                 }
             }
         }
-        for (; s < r_hi + 31; ++s) step(s, true);
         if (r_hi > r_lo) {  // the rows after the last complete group (and that group once more)
             const int ga = (r_hi - 1) & ~7;
             if (ga - 8 >= g_lo) dd_flush8(ws, lane, dlane, ga - 8);
@@ -427,14 +355,13 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
     }
 }
 
-// forward sweep: jobs[0..n) with their direction-word offsets dir_off[] into dirbuf and their plan bytes
-// (columns per lane | 0x80 = query profile) from vsk_dd_plan_kernel
+// forward sweep: jobs[0..n) with their direction-word offsets dir_off[] into dirbuf
 __global__ void __maxnreg__(120)
 vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
                   const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
-                  const uint8_t *__restrict__ plan, const int *__restrict__ bounds, int batch, int64_t batch_words,
-                  int job_end, const uint8_t *__restrict__ dist, const uint16_t *__restrict__ gapnd, int *scratch,
-                  int scratch_stride, uint32_t *__restrict__ dirbuf, int *queue, int4 *out) {
+                  const int *__restrict__ bounds, int batch, int64_t batch_words, int job_end, int force,
+                  const uint8_t *__restrict__ dist, const uint16_t *__restrict__ gapnd, int *scratch, int scratch_stride,
+                  uint32_t *__restrict__ dirbuf, int *queue, int4 *out) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -454,16 +381,15 @@ vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restr
         if (!VSK_DP_DIRJOB(job.l2)) continue;
         const uint16_t *L = left_ids + job.left_off;
         const uint16_t *Tp = top_ids + job.top_off;
-        const int pl = plan[ji];
-        const int cpl = pl & 0x7f;
-        int nb = 0, na = 0;
-        const int mode = dd_setup(L, Tp, job.l1, job.l2, dist, s_gapnd, ws, my_rowrec, (pl & 0x80) != 0, cpl, nb, na);
+        int nb = 0;
+        const bool smemt = dd_setup(L, Tp, job.l1, job.l2, dist, s_gapnd, ws, my_rowrec, nb);
         uint32_t *dir = dirbuf + (dir_off[ji] - (int64_t)batch * batch_words);
-#define DD_DISPATCH(C)                                                                                        \
-    do {                                                                                                      \
-        if (mode == DD_QP) dd_pair<C, DD_QP>(job, Tp, dist, s_gapnd, ws, na, my_bscr, my_rowrec, dir, out);   \
-        else if (mode == DD_SMEMT) dd_pair<C, DD_SMEMT>(job, Tp, dist, s_gapnd, ws, na, my_bscr, my_rowrec, dir, out); \
-        else dd_pair<C, DD_GLOBAL>(job, Tp, dist, s_gapnd, ws, na, my_bscr, my_rowrec, dir, out);             \
+        int cpl, ns;
+        dd_plan(job.l2, force, cpl, ns);
+#define DD_DISPATCH(C)                                                                       \
+    do {                                                                                     \
+        if (smemt) dd_pair<C, true>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out); \
+        else dd_pair<C, false>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out);      \
     } while (0)
         if (cpl == 16) DD_DISPATCH(16);
         else if (cpl == 12) DD_DISPATCH(12);
@@ -530,8 +456,7 @@ __device__ __forceinline__ void dq_pair(const vsk_dp_job &job, const uint16_t *_
         const uint8_t *trow = s_ktab + (int)s_dense[id] * K;
         if (active) {
             if (glane == 0) lfd = dgd + gl;  // column 0, profile.h:2084-2090
-            const uint32_t qnone[CPL / 4] = {};
-            const uint32_t w = dd_row_cells<CPL, DD_SMEMT>(Hd, Hd, tb, gt, qnone, dgd, lfd, trow, gl);
+            const uint32_t w = dd_row_cells<CPL, true>(Hd, Hd, tb, gt, dgd, lfd, trow, gl);
             dgd = lfd;
             ring[r & 15] = w;
         }
@@ -624,7 +549,7 @@ vsk_dp_q8dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
 __global__ void __launch_bounds__(DT_THREADS)
 vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
                     const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
-                    const uint8_t *__restrict__ plan, const int *__restrict__ bounds, int batch, int64_t batch_words,
+                    const int *__restrict__ bounds, int batch, int64_t batch_words, int force,
                     const uint8_t *__restrict__ dist, const uint16_t *__restrict__ gapnd,
                     const uint32_t *__restrict__ dirbuf, int4 *out, vsk_dp_job *redo, int *redo_count, int q_begin) {
     __shared__ uint16_t s_gapnd[1024];
@@ -644,7 +569,9 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
         const uint16_t *Tp = top_ids + job.top_off;
         const uint32_t *dir = dirbuf + (off0 - (int64_t)batch * batch_words);
         const int l1p = (job.l1 + 7) & ~7;
-        const int cpl = (ji >= q_begin) ? dq_cpl(job.l2) : (plan[ji] & 0x7f);  // 8-lane job : sweep's plan
+        int cpl, ns;
+        if (ji >= q_begin) cpl = dq_cpl(job.l2);  // 8-lane job
+        else dd_plan(job.l2, force, cpl, ns);
         int r = job.l1, c = job.l2;
         int p1 = 0, sumw = 0, len = 0;
         // position of column c-1 inside the strips: strip*32 + lane, cell
@@ -729,55 +656,20 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
     }
 }
 
-// Plan + direction words of the warp-per-pair jobs [0, n_warp): one warp per job counts the distinct
-// compositions of the reference-side profile (that bounds the columns per lane a query profile allows),
-// dd_plan picks columns per lane / strips / table mode; plan[i] = cpl | 0x80 (query profile), words[i] = the
-// direction words the job needs (0 = not a job for this path).
-__global__ void __launch_bounds__(256)
-vsk_dd_plan_kernel(const uint16_t *__restrict__ left_ids, const vsk_dp_job *__restrict__ jobs, int n_warp,
-                   int64_t *__restrict__ words, uint8_t *__restrict__ plan, int force) {
-    __shared__ uint32_t s_bm[8][32];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int i = blockIdx.x * 8 + warp;
-    if (i >= n_warp) return;
+// direction words a job needs (0 = not a job for this path); jobs[q_begin..n) are the 8-lane jobs
+__global__ void vsk_dd_words_kernel(const vsk_dp_job *__restrict__ jobs, int n, int q_begin, int force,
+                                    int64_t *__restrict__ words) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
     const int l1 = jobs[i].l1, l2 = jobs[i].l2;
-    if (!VSK_DP_DIRJOB(l2)) {
-        if (lane == 0) { words[i] = 0; plan[i] = 0; }
+    const int64_t l1p = (l1 + 7) & ~7;
+    if (i >= q_begin) {
+        words[i] = DQ_G * l1p;
         return;
     }
-    s_bm[warp][lane] = 0;
-    __syncwarp();
-    const uint16_t *L = left_ids + jobs[i].left_off;
-    for (int k = lane; k < l1; k += 32) {
-        const int id = L[k];
-        atomicOr(&s_bm[warp][id >> 5], 1u << (id & 31));
-    }
-    __syncwarp();
-    int na = __popc(s_bm[warp][lane]);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) na += __shfl_xor_sync(DD_FULL, na, o);
-    if (lane == 0) {
-        int cpl, ns;
-        bool qp;
-        dd_plan(l2, na, cpl, ns, qp);
-        if (force) {  // tuning aid (VSK_DD_FORCE): columns per lane and table mode as told, where the alphabet allows
-            cpl = force & 0x7f;
-            ns = (l2 + 32 * cpl - 1) / (32 * cpl);
-            qp = (force & 0x80) && na <= DD_MAXNA && na * 32 * cpl <= DD_TBYTES;
-        }
-        const int64_t l1p = (l1 + 7) & ~7;
-        words[i] = (int64_t)ns * 32 * l1p;
-        plan[i] = (uint8_t)(cpl | (qp ? 0x80 : 0));
-    }
-}
-
-// direction words of the 8-lane jobs [q_begin, n)
-__global__ void vsk_dd_words8_kernel(const vsk_dp_job *__restrict__ jobs, int n, int q_begin,
-                                     int64_t *__restrict__ words) {
-    const int i = q_begin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int64_t l1p = (jobs[i].l1 + 7) & ~7;
-    words[i] = DQ_G * l1p;
+    int cpl, ns;
+    dd_plan(l2, force, cpl, ns);
+    words[i] = VSK_DP_DIRJOB(l2) ? (int64_t)ns * 32 * l1p : 0;
 }
 
 // bounds[b] = first job whose direction words start at or after b*batch_words (jobs of a batch are
@@ -846,26 +738,15 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     if ((rc = dd_reserve(ctx, 0, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_words))) return rc;
     if ((rc = dd_reserve(ctx, 1, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_off))) return rc;
     if ((rc = dd_reserve(ctx, 2, tmp_bytes + 16, &d_tmp))) return rc;
-    uint8_t *d_plan = nullptr;
-    if ((rc = dd_reserve(ctx, 7, (size_t)n + 16, (void **)&d_plan))) return rc;
     VSK_CUDA(ctx, cudaStreamWaitEvent(s0, ctx->dd_ev[0], 0));
     VSK_CUDA(ctx, cudaMemsetAsync(d_words + n, 0, sizeof(int64_t), s0));
-    if (n_warp > 0) {
-        static const int force = [] {  // e.g. VSK_DD_FORCE=qp16, t12 (tuning aid)
-            const char *e = getenv("VSK_DD_FORCE");
-            if (!e || !*e) return 0;
-            const bool qp = (e[0] == 'q');
-            const int c = atoi(e + (qp ? 2 : 1));
-            return (c == 8 || c == 12 || c == 16) ? (c | (qp ? 0x80 : 0)) : 0;
-        }();
-        vsk_dd_plan_kernel<<<(unsigned)((n_warp + 7) / 8), 256, 0, s0>>>(d_left_ids, d_jobs, (int)n_warp, d_words, d_plan,
-                                                                        force);
-        ctx->launches++;
-    }
-    if (n_q8 > 0) {
-        vsk_dd_words8_kernel<<<(unsigned)((n_q8 + 255) / 256), 256, 0, s0>>>(d_jobs, (int)n, (int)n_warp, d_words);
-        ctx->launches++;
-    }
+    static const int force = [] {  // tuning aid: VSK_DD_FORCE=8|12|16 fixes the columns per lane of the sweep
+        const char *e = getenv("VSK_DD_FORCE");
+        const int c = e ? atoi(e) : 0;
+        return (c == 8 || c == 12 || c == 16) ? c : 0;
+    }();
+    vsk_dd_words_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s0>>>(d_jobs, (int)n, (int)n_warp, force, d_words);
+    ctx->launches++;
     VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
     ctx->launches += 2;
     int64_t total = 0, off_q8 = 0;  // all words; words before the first 8-lane job
@@ -944,8 +825,8 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
                 VSK_CUDA(ctx, cudaEventCreate(&pe1));
                 VSK_CUDA(ctx, cudaEventRecord(pe0, st));
             }
-            vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, dd_smem, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_plan, d_bounds,
-                                                                    b, batch_words, (int)n_warp, ctx->d_dist,
+            vsk_dp_dir_kernel<<<grid, DD_WARPS * 32, dd_smem, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
+                                                                    batch_words, (int)n_warp, force, ctx->d_dist,
                                                                     ctx->d_gapnd, scr, stride, dir, d_queue, d_out);
             ctx->launches++;
             if (ctx->profile) {
@@ -960,10 +841,9 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
                 ctx->d_tiny_ktab, K, ctx->d_gapnd, dir, d_queue8 + b, d_out);
             ctx->launches++;
         }
-        vsk_dp_trace_kernel<<<ctx->sm_count * 16, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_plan,
-                                                                       d_bounds, b, batch_words, ctx->d_dist,
-                                                                       ctx->d_gapnd, dir, d_out, *redo, *redo_count,
-                                                                       (int)n_warp);
+        vsk_dp_trace_kernel<<<ctx->sm_count * 16, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
+                                                                       batch_words, force, ctx->d_dist, ctx->d_gapnd,
+                                                                       dir, d_out, *redo, *redo_count, (int)n_warp);
         ctx->launches++;
     }
     VSK_CUDA(ctx, cudaGetLastError());
