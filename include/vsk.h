@@ -188,6 +188,14 @@ int vsk_trset_load_leb36(const char *path, int is_read, int maxflank, int option
  * temporary + rename.  The redundancy state is not cached: apply the .rotindex afterwards as usual. */
 int vsk_trset_load_leb36_cached(const char *path, int is_read, int maxflank, int option_r, int reflen,
                                 const char *cache_path, vsk_trset **out, int *from_cache);
+/* The same file tokenised only (second half): the LEB36 profile fields and the flank
+ * text stay as they are in the file and are decoded by the GPU when the set is uploaded
+ * (vsk_reads_upload / vsk_proclu_run): LEB36ToInt (profile.h:786-807), the consensus
+ * (getConcensusFromProfile, :280-322) and the flank clean-up / reversal / complement (:667-695).  The
+ * host keeps keys, pattern sizes and lengths; the consensus lengths arrive with the first upload.  For
+ * read sets: vsk_refs_create needs the consensus strings on the host and refuses a raw set.        */
+int vsk_trset_load_leb36_raw(const char *path, int is_read, int maxflank, int option_r, int reflen,
+                             vsk_trset **out);
 /* same from arrays: prof_off[2n+1] into ids; flank_off[2n+1] into flanks (left,
  * right per record, as they stand in the file: left NOT reversed)             */
 int vsk_trset_from_arrays(int32_t n, const int32_t *key, const int32_t *patlen,

@@ -81,3 +81,57 @@ def test_sharding_invariance_and_clustering(ctx, workload, tmp_path):
             out.add(frozenset(int(t[:-1]) for t in line.split()[1:]))
         return out
     assert clusters(whole, "a.clu") == clusters(np.concatenate(parts[::-1]), "b.clu")
+
+
+def test_links_left_on_device_equal_host_links(ctx, workload):
+    """vsk_proclu_result_links_dev: the table the multi-GPU merge sends is the table the host gets, also
+    when the run is cut into chunks (the chunks append to the device copy); viewed as a torch tensor
+    without a copy (what dist.LinkGatherer takes)"""
+    import torch
+
+    import vntrseek_b200 as v
+    from vntrseek_b200._lib import LINK_DTYPE
+    refs, reads, idx = workload
+    ts = v.TRSetHandle.from_packed(reads, is_read=True)
+    host, st = v.proclu(ctx, idx, ts, key_budget=200000)
+    host = np.array(host)
+    dl, st2 = v.proclu(ctx, idx, ts, key_budget=200000, links_on_device=True)
+    assert len(dl) == len(host) == st2["confirmed"] and st2["chunks"] > 3
+    t = dl.tensor()
+    assert t.is_cuda and t.dtype == torch.int32 and tuple(t.shape) == (len(host), 7)
+    assert t.data_ptr() == dl.ptr      # a view of the library's buffer, not a copy
+    got = t.cpu().numpy().reshape(-1).view(LINK_DTYPE)
+    assert (got == host).all()
+    ts.close()
+
+
+def test_gpu_decoded_read_file_equals_text_parsed(ctx, workload, tmp_path):
+    """vsk_trset_load_leb36_raw: the read file only tokenised on the host, LEB36 digits / consensus / flank
+    clean-up done by the GPU at upload -- same links, same counters as the host parser's set (mixed-case
+    and non-ACGT flank characters, dash-majority columns, rotindex included)"""
+    import vntrseek_b200 as v
+    refs, reads, idx = workload
+    path = str(tmp_path / "reads.leb36")
+    sub = reads.slice(0, 6000)
+    sub.write_leb36(path)
+    # spoil some flanks: lower case and non-ACGT characters must come out as the host parser has them
+    lines = open(path).read().splitlines()
+    for k in range(0, len(lines), 7):
+        f = lines[k].rsplit(" ", 1)
+        fl = f[1]
+        lines[k] = f[0] + " " + fl[: len(fl) // 2].lower() + fl[len(fl) // 2:].replace("A", "R", 1)
+    open(path, "w").write("\n".join(lines) + "\n")
+    a = v.TRSetHandle.from_file(path, is_read=True, maxflank=50)
+    b = v.TRSetHandle.from_file(path, is_read=True, maxflank=50, raw=True)
+    la, sa = v.proclu(ctx, idx, a)
+    lb, sb = v.proclu(ctx, idx, b)
+    keys = ("candidates_considered", "lcs_alignments", "profile_alignments", "profile_alignments_success", "confirmed")
+    assert [sa[k] for k in keys] == [sb[k] for k in keys]
+    assert len(la) > 500 and (np.array(la) == np.array(lb)).all()
+    # and resident, twice (the host learnt the consensus lengths at the first upload)
+    rb = v.ResidentReads(ctx, b)
+    lc, sc = v.proclu(ctx, idx, rb)
+    assert (np.array(lc) == np.array(la)).all()
+    rb.close()
+    a.close()
+    b.close()

@@ -226,3 +226,31 @@ def test_psearch_ref_to_ref_mode(tmp_path, dst_file, reflen):
     m1 = sorted(open(os.path.join(a, "reads.leb36.map")).read().splitlines())
     m2 = sorted(open(os.path.join(b, "reads.leb36.map")).read().splitlines())
     assert len(m1) > 50 and m1 == m2
+
+
+@pytest.mark.parametrize("switch", ["VSK_GPU_DECODE", "VSK_TRSET_CACHE"])
+def test_loader_switches_give_the_same_files(tmp_path, dst_file, switch):
+    """VSK_GPU_DECODE=1 (read file tokenised on the host, decoded on the GPU) and VSK_TRSET_CACHE=1 (parsed
+    arrays kept in <file>.vsktr; run twice: written, then read back): same counters, same .clu"""
+    from conftest import GOLDEN
+    g = os.path.join(GOLDEN, "psearch_small")
+    want = None
+    for run_no, val in enumerate((None, "1", "1")):
+        w = str(tmp_path / "w")
+        if run_no == 0 or switch != "VSK_TRSET_CACHE":
+            shutil.rmtree(w, ignore_errors=True)
+            shutil.copytree(g, w)
+        if os.path.exists(os.path.join(w, "reads.leb36.clu")):
+            os.remove(os.path.join(w, "reads.leb36.clu"))
+        env = dict(os.environ)
+        if val is not None:
+            env[switch] = val
+        rc, _, log = run(os.path.join(OUR_BIN, "psearch.exe"), ["reference.leb36", "reads.leb36", dst_file, 88, 0, 50], w,
+                         env=env)
+        assert rc == 0, log[-500:]
+        got = (parse_counters(log), open(os.path.join(w, "reads.leb36.clu")).read())
+        want = want or got
+        assert got == want, (switch, run_no)
+        if switch == "VSK_TRSET_CACHE" and run_no > 0:
+            assert os.path.exists(os.path.join(w, "reads.leb36.vsktr")) and os.path.exists(os.path.join(w, "reference.leb36.vsktr"))
+    assert want[0] == parse_counters(open(os.path.join(g, "ref.log")).read())

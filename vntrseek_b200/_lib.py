@@ -98,6 +98,7 @@ LINK_DTYPE = np.dtype([("refkey", np.int32), ("readkey", np.int32), ("dir", np.i
 def _declare2(L):
     vp = C.c_void_p
     L.vsk_trset_load_leb36.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    L.vsk_trset_load_leb36_raw.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
     L.vsk_trset_load_leb36_cached.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.POINTER(vp),
                                               C.POINTER(C.c_int)]
     L.vsk_trset_from_arrays.argtypes = [C.c_int32, _p(np.int32), _p(np.int32), _p(np.int64), _p(np.uint16),

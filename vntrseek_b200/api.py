@@ -203,12 +203,14 @@ class TRSetHandle:
         self.h = h
 
     @classmethod
-    def from_file(cls, path, is_read, maxflank=50, option_r=0, reflen=50, rotindex=True, cache_path=None):
+    def from_file(cls, path, is_read, maxflank=50, option_r=0, reflen=50, rotindex=True, cache_path=None, raw=False):
         """cache_path: keep / use the parsed arrays in that binary file (vsk_trset_load_leb36_cached);
         `.from_cache` tells whether the text was parsed (False) or the file served (True)"""
         h = C.c_void_p()
         hit = C.c_int(0)
-        if cache_path:
+        if raw:  # tokenised only; the GPU decodes profiles and flanks at upload (vsk_trset_load_leb36_raw)
+            rc = lib().vsk_trset_load_leb36_raw(path.encode(), int(is_read), maxflank, option_r, reflen, C.byref(h))
+        elif cache_path:
             rc = lib().vsk_trset_load_leb36_cached(path.encode(), int(is_read), maxflank, option_r, reflen,
                                                    os.fsencode(cache_path), C.byref(h), C.byref(hit))
         else:
@@ -321,7 +323,7 @@ class DeviceLinks:
     def __init__(self, ptr, n, device):
         self.ptr, self.n, self.device = ptr, n, device
         nf = LINK_DTYPE.itemsize // 4
-        self.__cuda_array_interface__ = {"shape": (n, nf), "typestr": "<i4", "data": (ptr or 0, True), "version": 2}
+        self.__cuda_array_interface__ = {"shape": (n, nf), "typestr": "<i4", "data": (ptr or 0, False), "version": 2}
 
     def __len__(self):
         return self.n

@@ -26,6 +26,9 @@ static void die(const char *msg) {
  * back when the text has not changed since); unset = parse the text in every process as the reference does */
 static int load_profiles(const char *path, int is_read, int maxflank, int option_r, int reflen, vsk_trset **out) {
     const char *e = getenv("VSK_TRSET_CACHE");
+    const char *g = getenv("VSK_GPU_DECODE"); /* =1: read files are only tokenised here, decoded on the GPU */
+    if (is_read && g && *g && strcmp(g, "0") != 0)
+        return vsk_trset_load_leb36_raw(path, is_read, maxflank, option_r, reflen, out);
     if (e && *e && strcmp(e, "0") != 0) {
         char cache[1200];
         snprintf(cache, sizeof cache, "%s.vsktr", path);

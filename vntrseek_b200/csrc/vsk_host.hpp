@@ -35,6 +35,15 @@ struct vsk_trset {
     std::vector<int32_t> rot_off, rot_mem;
     bool rot_flat = false;
     std::vector<void *> pinned;  // host ranges registered with cudaHostRegister (vsk_trset_pin)
+    // Raw mode (vsk_trset_load_leb36_raw): profiles and flanks are still the file's text and are decoded on
+    // the device when the set is uploaded (LEB36 digits -> ids, consensus, flank clean-up).  ids / cons / fl
+    // stay empty on the host; prof_off, fl_off, leftlen, rightlen are known from the field lengths;
+    // cons_off is filled in by the first upload (raw_decoded).
+    bool raw = false, raw_decoded = false;
+    std::vector<char> raw_text;        // the whole file
+    std::vector<int64_t> raw_prof;     // [2n] offset of each profile's LEB36 field
+    std::vector<int64_t> raw_flank;    // [2n] offset of the left / right flank text of each record
+    std::vector<int32_t> raw_flen;     // [2n] their lengths
 };
 
 // Seed geometry per TRANGE (psearch.c:161-318)

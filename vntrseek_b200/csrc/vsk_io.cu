@@ -103,6 +103,39 @@ static void finish_record(vsk_trset &ts, int32_t key, int32_t patlen, const std:
     }
 }
 
+// raw mode: the record's offsets and lengths only (what finish_record derives from lengths alone)
+static void finish_record_raw(vsk_trset &ts, int32_t key, int32_t patlen, int64_t off_fwd, int64_t len_fwd,
+                              int64_t off_rc, int64_t len_rc, int64_t off_left, int32_t len_left, int64_t off_right,
+                              int32_t len_right, int maxflank, bool option_r, int reflen) {
+    ts.key.push_back(key);
+    ts.patlen.push_back(patlen);
+    ts.raw_prof.push_back(off_fwd);
+    ts.raw_prof.push_back(off_rc);
+    ts.prof_off.push_back(ts.prof_off.back() + len_fwd);
+    ts.prof_off.push_back(ts.prof_off.back() + len_rc);
+    ts.cons_off.push_back(0);  // known after the device has decoded the profiles
+    ts.cons_off.push_back(0);
+    ts.raw_flank.push_back(off_left);
+    ts.raw_flank.push_back(off_right);
+    ts.raw_flen.push_back(len_left);
+    ts.raw_flen.push_back(len_right);
+    // forward: left (reversed), right; rc: left = complement(right), right = complement(left)
+    const int32_t parts[4] = {len_left, len_right, len_right, len_left};
+    for (int k = 0; k < 4; ++k) ts.fl_off.push_back(ts.fl_off.back() + parts[k]);
+    for (int o = 0; o < 2; ++o) {
+        int ll = parts[2 * o], rl2 = parts[2 * o + 1];
+        if (option_r) {  // profile.h:711-715
+            ll = std::min(ll, reflen);
+            rl2 = std::min(rl2, reflen);
+        } else if (ts.is_read) {  // profile.h:723-728
+            ll = std::min(ll, maxflank);
+            rl2 = std::min(rl2, maxflank);
+        }
+        ts.leftlen.push_back(ll);
+        ts.rightlen.push_back(rl2);
+    }
+}
+
 static void init_rot(vsk_trset &ts) {
     ts.n = (int32_t)ts.key.size();
     ts.master.assign(ts.n, 1);
@@ -130,7 +163,7 @@ static vsk_trset *new_trset(bool is_read) {
 // first record it cannot parse, psearch.c:332-345); `ragged` = a record was not on one line or the
 // range ended inside a record, i.e. line starts are not record starts in this file.
 static int parse_leb36_range(char *p, const char *path, int maxflank, bool option_r, int reflen, vsk_trset &ts,
-                             bool &stopped, bool &ragged) {
+                             bool &stopped, bool &ragged, const char *raw_base = nullptr) {
     stopped = ragged = false;
     auto next_token = [&](char *&tok, size_t &len) -> bool {
         while (*p && isspace((unsigned char)*p)) ++p;
@@ -163,6 +196,15 @@ static int parse_leb36_range(char *p, const char *path, int maxflank, bool optio
         if (e == tok[4]) break;
         if (proflen <= 0 || proflenrc <= 0) break;
         if (len[5] != (size_t)(2 * proflen) || len[6] != (size_t)(2 * proflenrc)) break;
+        if (raw_base) {  // raw mode: keep where the fields are, decode on the device
+            const char *bar = (const char *)memchr(tok[11], '|', len[11]);
+            if (!bar) break;  // "No flanks specified!" -> NULL -> stop
+            finish_record_raw(ts, (int32_t)key, (int32_t)patlen, tok[5] - raw_base, proflen, tok[6] - raw_base, proflenrc,
+                              tok[11] - raw_base, (int32_t)(bar - tok[11]), bar + 1 - raw_base,
+                              (int32_t)(tok[11] + len[11] - (bar + 1)), maxflank, option_r, reflen);
+            stopped = false;
+            continue;
+        }
         fwd.resize((size_t)proflen);
         rc.resize((size_t)proflenrc);
         bool bad = false;
@@ -204,10 +246,27 @@ static void append_trset(vsk_trset &a, const vsk_trset &b) {
     for (size_t i = 1; i < b.fl_off.size(); ++i) a.fl_off.push_back(b.fl_off[i] + f0);
     a.leftlen.insert(a.leftlen.end(), b.leftlen.begin(), b.leftlen.end());
     a.rightlen.insert(a.rightlen.end(), b.rightlen.begin(), b.rightlen.end());
+    a.raw_prof.insert(a.raw_prof.end(), b.raw_prof.begin(), b.raw_prof.end());  // offsets into the one shared text
+    a.raw_flank.insert(a.raw_flank.end(), b.raw_flank.begin(), b.raw_flank.end());
+    a.raw_flen.insert(a.raw_flen.end(), b.raw_flen.begin(), b.raw_flen.end());
 }
+
+static int load_leb36(const char *path, int is_read, int maxflank, int option_r, int reflen, bool raw, vsk_trset **out);
 
 extern "C" int vsk_trset_load_leb36(const char *path, int is_read, int maxflank, int option_r, int reflen,
                                     vsk_trset **out) {
+    return load_leb36(path, is_read, maxflank, option_r, reflen, false, out);
+}
+
+// The same file, tokenised only: the profiles and flanks stay text and are decoded by the GPU when the set is
+// uploaded (vsk_reads_upload / vsk_proclu_run).  For read sets; a reference set needs its consensus strings
+// on the host (seed index) and is refused by vsk_refs_create in this form.
+extern "C" int vsk_trset_load_leb36_raw(const char *path, int is_read, int maxflank, int option_r, int reflen,
+                                        vsk_trset **out) {
+    return load_leb36(path, is_read, maxflank, option_r, reflen, true, out);
+}
+
+static int load_leb36(const char *path, int is_read, int maxflank, int option_r, int reflen, bool raw, vsk_trset **out) {
     if (!path || !out) return VSK_ERR_ARG;
     *out = nullptr;
     FILE *fp = fopen(path, "rb");
@@ -252,7 +311,8 @@ extern "C" int vsk_trset_load_leb36(const char *path, int is_read, int maxflank,
                 bool st = false, rg = false;
                 char *b = cut[(size_t)k] + (k > 0 && cut[(size_t)k] < buf.data() + sz ? 1 : 0);
                 if (b > cut[(size_t)k + 1]) b = cut[(size_t)k + 1];
-                rcs[(size_t)k] = parse_leb36_range(b, path, maxflank, option_r != 0, reflen, *part[(size_t)k], st, rg);
+                rcs[(size_t)k] = parse_leb36_range(b, path, maxflank, option_r != 0, reflen, *part[(size_t)k], st, rg,
+                                                   raw ? buf.data() : nullptr);
                 stopped[(size_t)k] = st;
                 ragged[(size_t)k] = rg;
             });
@@ -280,11 +340,16 @@ extern "C" int vsk_trset_load_leb36(const char *path, int is_read, int maxflank,
     }
     if (!done) {
         bool st, rg;
-        const int rc = parse_leb36_range(buf.data(), path, maxflank, option_r != 0, reflen, *ts, st, rg);
+        const int rc = parse_leb36_range(buf.data(), path, maxflank, option_r != 0, reflen, *ts, st, rg,
+                                         raw ? buf.data() : nullptr);
         if (rc != VSK_OK) {
             *out = ts;
             return rc;
         }
+    }
+    if (raw) {
+        ts->raw = true;
+        ts->raw_text.swap(buf);
     }
     init_rot(*ts);
     *out = ts;

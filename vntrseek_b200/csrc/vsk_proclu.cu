@@ -136,6 +136,86 @@ __global__ void __launch_bounds__(256) vsk_pack_consensus_kernel(DevTR t, int64_
     if (lane == 0) t.cons_cnt[p] = cnt;
 }
 
+// ---- decoding a raw TR set on the device (vsk_trset_load_leb36_raw) --------------------------------
+// What ReadProfileWithRC does per record after tokenising the line (profile.h:546-729): two LEB36
+// characters per column -> composition id (LEB36ToInt, :786-807), the consensus = majority symbol of every
+// column that is not dash-majority (getConcensusFromProfile, :280-322), and the flanks upper-cased with
+// non-ACGT -> N, the left one reversed, the reverse-complement profile's flanks complemented and swapped
+// (:667-695).  c_cons_sym[id] = 0..3 for A,C,G,T, 4 for a dash-majority column (first maximum wins).
+__constant__ int8_t c_cons_sym[1024];
+
+__device__ __forceinline__ int leb36_digit_dev(int c) { return (c < 65) ? (c & 0xF) : ((c & 0x1F) + 9); }
+
+// warp per profile.  pass 0: conslen[p] = consensus length (and the id range check); pass 1: ids and
+// consensus characters are written (cons_off known by then).
+template <int PASS>
+__global__ void __launch_bounds__(256)
+vsk_leb36_decode_kernel(const uint8_t *__restrict__ text, const int64_t *__restrict__ raw_prof,
+                        const int64_t *__restrict__ prof_off, const int64_t *__restrict__ cons_off, int64_t nprof,
+                        uint16_t *__restrict__ ids, uint8_t *__restrict__ cons, int32_t *__restrict__ conslen,
+                        int *__restrict__ err) {
+    const int64_t p = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (p >= nprof) return;
+    const uint8_t *src = text + raw_prof[p];
+    const int64_t o = prof_off[p];
+    const int len = (int)(prof_off[p + 1] - o);
+    int64_t cpos = PASS ? cons_off[p] : 0;
+    int total = 0;
+    for (int base = 0; base < len; base += 32) {
+        const int c = base + lane;
+        int v = 0, sym = 4;
+        if (c < len) {
+            v = leb36_digit_dev(src[2 * c]) + 36 * leb36_digit_dev(src[2 * c + 1]);
+            if (v < 0 || v > 1000) {
+                *err = 1;
+                v = 0;
+            }
+            sym = c_cons_sym[v];
+        }
+        const unsigned keep = __ballot_sync(0xffffffffu, sym != 4);
+        if (PASS && c < len) {
+            ids[o + c] = (uint16_t)v;
+            if (sym != 4) cons[cpos + __popc(keep & ((1u << lane) - 1u))] = (uint8_t)"ACGT"[sym];
+        }
+        cpos += __popc(keep);
+        total += __popc(keep);
+    }
+    if (!PASS && lane == 0) conslen[p] = total;
+}
+
+__device__ __forceinline__ uint8_t flank_clean(uint8_t c) {  // profile.h:667-685
+    if (c >= 'a' && c <= 'z') c -= 32;
+    return (c == 'A' || c == 'C' || c == 'G' || c == 'T') ? c : (uint8_t)'N';
+}
+__device__ __forceinline__ uint8_t flank_comp(uint8_t c) {
+    return c == 'A' ? 'T' : c == 'C' ? 'G' : c == 'G' ? 'C' : c == 'T' ? 'A' : c;
+}
+
+// warp per record: the four flank strings of its two profiles
+__global__ void __launch_bounds__(256)
+vsk_flank_decode_kernel(const uint8_t *__restrict__ text, const int64_t *__restrict__ raw_flank,
+                        const int32_t *__restrict__ raw_flen, const int64_t *__restrict__ fl_off, int64_t n,
+                        uint8_t *__restrict__ fl) {
+    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const uint8_t *L = text + raw_flank[2 * i], *R = text + raw_flank[2 * i + 1];
+    const int ll = raw_flen[2 * i], rl = raw_flen[2 * i + 1];
+    uint8_t *fwd_l = fl + fl_off[4 * i], *fwd_r = fl + fl_off[4 * i + 1], *rc_l = fl + fl_off[4 * i + 2],
+            *rc_r = fl + fl_off[4 * i + 3];
+    for (int k = lane; k < ll; k += 32) {
+        const uint8_t c = flank_clean(L[ll - 1 - k]);  // forward left = the file's left flank reversed
+        fwd_l[k] = c;
+        rc_r[k] = flank_comp(c);
+    }
+    for (int k = lane; k < rl; k += 32) {
+        const uint8_t c = flank_clean(R[k]);
+        fwd_r[k] = c;
+        rc_l[k] = flank_comp(c);
+    }
+}
+
 static int upload_raw(vsk_ctx *ctx, std::vector<void *> &allocs, const uint8_t *h, size_t n, uint8_t **d,
                       int64_t *bytes) {
     VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)d, n + 64, ctx->pool, ctx->stream));
@@ -166,6 +246,99 @@ int vsk_trset_check_limits(vsk_ctx *ctx, const vsk_trset *ts) {
     return VSK_OK;
 }
 
+int vsk_trset_check_limits(vsk_ctx *ctx, const vsk_trset *ts);
+// Uploads a raw TR set: the file's text goes to the device and is decoded there; the consensus lengths come
+// back so that the host knows cons_off (first upload only).
+static int decode_raw_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads *r) {
+    static uint64_t sym_set = 0;  // per device
+    if (!((sym_set >> (ctx->device & 63)) & 1)) {
+        int8_t sym[1024];
+        memset(sym, 4, sizeof sym);
+        int id = 0;
+        for (int a = 0; a <= 10; ++a)
+            for (int c = 0; c <= 10; ++c)
+                for (int g = 0; g <= 10; ++g)
+                    for (int t = 0; t <= 10; ++t) {
+                        const int d = 10 - a - c - g - t;
+                        if (d < 0) continue;
+                        const int cnt[5] = {a, c, g, t, d};
+                        int sel = 0, mx = 0;  // getConcensusFromProfile, profile.h:291-298
+                        for (int j = 0; j < 5; ++j)
+                            if (cnt[j] > mx) { mx = cnt[j]; sel = j; }
+                        sym[id++] = (int8_t)sel;
+                    }
+        VSK_CUDA(ctx, cudaMemcpyToSymbol(c_cons_sym, sym, sizeof sym));
+        sym_set |= 1ull << (ctx->device & 63);
+    }
+    cudaStream_t st = ctx->stream;
+    const int64_t np = 2 * (int64_t)ts->n;
+    int rc;
+    uint8_t *d_text = nullptr;
+    int64_t *d_raw_prof = nullptr, *d_raw_flank = nullptr;
+    int32_t *d_raw_flen = nullptr, *d_conslen = nullptr;
+    int *d_err = nullptr;
+    std::vector<void *> tmp;  // freed when the decode is done
+    if ((rc = upload_raw(ctx, tmp, reinterpret_cast<const uint8_t *>(ts->raw_text.data()), ts->raw_text.size(), &d_text,
+                         &r->h2d_bytes)) ||
+        (rc = upload_vec(ctx, tmp, ts->raw_prof, &d_raw_prof, &r->h2d_bytes)) ||
+        (rc = upload_vec(ctx, tmp, ts->raw_flank, &d_raw_flank, &r->h2d_bytes)) ||
+        (rc = upload_vec(ctx, tmp, ts->raw_flen, &d_raw_flen, &r->h2d_bytes)) ||
+        (rc = upload_vec(ctx, r->allocs, ts->prof_off, &r->d.prof_off, &r->h2d_bytes)) ||
+        (rc = upload_vec(ctx, r->allocs, ts->fl_off, &r->d.fl_off, &r->h2d_bytes))) {
+        for (void *p : tmp) cudaFreeAsync(p, st);
+        return rc;
+    }
+    auto fail = [&](int code) {
+        for (void *p : tmp) cudaFreeAsync(p, st);
+        return code;
+    };
+#define RAW_CUDA(call)                                                                                          \
+    do {                                                                                                        \
+        cudaError_t e__ = (call);                                                                               \
+        if (e__ != cudaSuccess)                                                                                 \
+            return fail(vsk_fail(ctx, VSK_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__))); \
+    } while (0)
+    RAW_CUDA(cudaMallocFromPoolAsync((void **)&d_conslen, sizeof(int32_t) * (size_t)(np + 1), ctx->pool, st));
+    tmp.push_back(d_conslen);
+    RAW_CUDA(cudaMallocFromPoolAsync((void **)&d_err, sizeof(int), ctx->pool, st));
+    tmp.push_back(d_err);
+    RAW_CUDA(cudaMemsetAsync(d_err, 0, sizeof(int), st));
+    RAW_CUDA(cudaMallocFromPoolAsync((void **)&r->d.ids, sizeof(uint16_t) * (size_t)(ts->prof_off.back() + 8), ctx->pool, st));
+    r->allocs.push_back(r->d.ids);
+    RAW_CUDA(cudaMallocFromPoolAsync((void **)&r->d.fl, (size_t)ts->fl_off.back() + 64, ctx->pool, st));
+    r->allocs.push_back(r->d.fl);
+    const unsigned gp = (unsigned)((np * 32 + 255) / 256), gr = (unsigned)(((int64_t)ts->n * 32 + 255) / 256);
+    if (np) {
+        vsk_leb36_decode_kernel<0><<<gp, 256, 0, st>>>(d_text, d_raw_prof, r->d.prof_off, nullptr, np, nullptr, nullptr,
+                                                      d_conslen, d_err);
+        vsk_flank_decode_kernel<<<gr, 256, 0, st>>>(d_text, d_raw_flank, d_raw_flen, r->d.fl_off, ts->n, r->d.fl);
+        ctx->launches += 2;
+    }
+    std::vector<int32_t> conslen((size_t)np);
+    int herr = 0;
+    if (np) RAW_CUDA(cudaMemcpyAsync(conslen.data(), d_conslen, sizeof(int32_t) * (size_t)np, cudaMemcpyDeviceToHost, st));
+    RAW_CUDA(cudaMemcpyAsync(&herr, d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+    RAW_CUDA(cudaStreamSynchronize(st));
+    if (herr) return fail(vsk_fail(ctx, VSK_ERR_ARG, "composition id outside 0..1000 in the profile file"));
+    vsk_trset *mt = const_cast<vsk_trset *>(ts);
+    if (!ts->raw_decoded) {
+        for (int64_t p = 0; p < np; ++p) mt->cons_off[(size_t)p + 1] = mt->cons_off[(size_t)p] + conslen[(size_t)p];
+        mt->raw_decoded = true;
+    }
+    if ((rc = upload_vec(ctx, r->allocs, ts->cons_off, &r->d.cons_off, &r->h2d_bytes))) return fail(rc);
+    RAW_CUDA(cudaMallocFromPoolAsync((void **)&r->d.cons, (size_t)ts->cons_off.back() + 64, ctx->pool, st));
+    r->allocs.push_back(r->d.cons);
+    if (np) {
+        vsk_leb36_decode_kernel<1><<<gp, 256, 0, st>>>(d_text, d_raw_prof, r->d.prof_off, r->d.cons_off, np, r->d.ids,
+                                                      r->d.cons, nullptr, d_err);
+        ctx->launches++;
+    }
+    RAW_CUDA(cudaGetLastError());
+#undef RAW_CUDA
+    for (void *p : tmp) cudaFreeAsync(p, st);
+    return vsk_trset_check_limits(ctx, ts);  // the consensus lengths are known now
+}
+
 static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
     *out = nullptr;
     if (int lim = vsk_trset_check_limits(ctx, ts)) return lim;
@@ -190,8 +363,13 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
 #define UPB(field, vec)                                                                                   \
     if ((rc = upload_raw(ctx, r->allocs, reinterpret_cast<const uint8_t *>((vec).data()), (vec).size(),    \
                          &r->d.field, &r->h2d_bytes))) { *out = r; return rc; }
-    UP(prof_off, ts->prof_off) UP(cons_off, ts->cons_off) UP(fl_off, ts->fl_off) UP(ids, ts->ids)
-    UPB(cons, ts->cons) UPB(fl, ts->fl) UP(leftlen, ts->leftlen) UP(rightlen, ts->rightlen) UP(patlen, ts->patlen)
+    if (ts->raw) {
+        if ((rc = decode_raw_trset(ctx, ts, r))) { *out = r; return rc; }
+    } else {
+        UP(prof_off, ts->prof_off) UP(cons_off, ts->cons_off) UP(fl_off, ts->fl_off) UP(ids, ts->ids)
+        UPB(cons, ts->cons) UPB(fl, ts->fl)
+    }
+    UP(leftlen, ts->leftlen) UP(rightlen, ts->rightlen) UP(patlen, ts->patlen)
     UP(key, ts->key) UP(rot_off, ts->rot_off) UP(rot_mem, ts->rot_mem) UP(dir, ts->dir) UP(master, ts->master)
 #undef UP
 #undef UPB
@@ -215,7 +393,7 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
     }
     VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     *out = r;
-    return vsk_id_presence(ctx, r->d.ids, (int64_t)ts->ids.size(), &r->present);
+    return vsk_id_presence(ctx, r->d.ids, ts->prof_off.back(), &r->present);
 }
 
 static void free_reads(vsk_reads *r) {
@@ -244,6 +422,7 @@ extern "C" int vsk_refs_create(vsk_ctx *ctx, const vsk_trset *refs, vsk_refs **o
 extern "C" int vsk_refs_create_cached(vsk_ctx *ctx, const vsk_trset *refs, const char *cache_path, vsk_refs **out) {
     if (!ctx || !refs || !out) return VSK_ERR_ARG;
     *out = nullptr;
+    if (refs->raw) return vsk_fail(ctx, VSK_ERR_ARG, "a raw (GPU-decoded) TR set cannot be the reference set: the seed index needs its consensus strings on the host");
     VSK_CUDA(ctx, cudaSetDevice(ctx->device));
     vsk_refindex_host hi;
     std::string err;
@@ -1288,7 +1467,7 @@ extern "C" int vsk_proclu_run_resident(vsk_ctx *ctx, const vsk_refs *R, const vs
         cudaError_t e;
         uint64_t *wcache;  // one word per consensus character of the reads: the seed windows the count pass found
         if ((e = S.get(&cnt, (size_t)nprof + 1)) != cudaSuccess || (e = S.get(&off, (size_t)nprof + 1)) != cudaSuccess ||
-            (e = S.get(&raw, 1)) != cudaSuccess || (e = S.get(&wcache, hq->cons.size() + 1)) != cudaSuccess) {
+            (e = S.get(&raw, 1)) != cudaSuccess || (e = S.get(&wcache, (size_t)hq->cons_off.back() + 1)) != cudaSuccess) {
             delete res;
             return vsk_fail(ctx, VSK_ERR_CUDA, "alloc: %s", cudaGetErrorString(e));
         }
