@@ -395,6 +395,7 @@ def ours(args, rank, world, local_rank):
     clocks = sampler.stop()
     ag_resident_ms = ag_ms[0] / K
     ag_ms[0] = 0.0
+    ag_phases = {k: val / (K + W) for k, val in gatherer.phase_ms.items()} if gatherer else {}
     # ---- end-to-end leg (host buffers in, links out) ----------------------------
     st2 = None
     for _ in range(min(W, 1)):
@@ -422,6 +423,18 @@ def ours(args, rank, world, local_rank):
         dist.all_reduce(tt, op=dist.ReduceOp.SUM)
         return float(tt.item())
 
+    def allgather_floats(x):
+        if world == 1:
+            return [x]
+        tt = torch.tensor([x], device="cuda", dtype=torch.float64)
+        outt = torch.zeros(world, device="cuda", dtype=torch.float64)
+        dist.all_gather_into_tensor(outt, tt)
+        return [float(v) for v in outt.tolist()]
+
+    rank_step_ms = allgather_floats(max(dev_ms, wall_ms) / K)
+    rank_ag_ms = allgather_floats(ag_resident_ms)
+    rank_scan_ms = allgather_floats(sum(stages.values()) / K)
+    rank_cells = allgather_floats(float(stats_cells["dp_cells"]))
     step_ms = allmax(max(dev_ms, wall_ms)) / K
     e2e_step_ms = allmax(e2e_ms) / K
     total_reads = allsum(float(len(reads)))
@@ -510,6 +523,11 @@ def ours(args, rank, world, local_rank):
         }
         if world > 1:
             line["allgather_ms_per_step"] = ag_resident_ms
+            line["allgather_note"] = ("CUDA events around the merge on every rank, max over ranks: it includes the time a "
+                                      "rank waits for the slowest rank's scan to finish (per_rank below)")
+            line["per_rank"] = {"ms_per_step": rank_step_ms, "scan_ms_per_step": rank_scan_ms,
+                                "allgather_ms_per_step": rank_ag_ms, "dp_cells_per_step": rank_cells,
+                                "rank0_merge_phases_host_ms": ag_phases}
         if parity is not None:
             line["parity_at_scale"] = parity
             ok = parity["counters_equal"] and parity["clu_equal"]

@@ -128,8 +128,17 @@ int vsk_pair_dp_cyclic(vsk_ctx *ctx, const vsk_profset *left_set, const vsk_prof
  * (l1, the reference-side profile) per pair; larger requests return VSK_ERR_ARG with a
  * message and do nothing.  The call makes no cudaMalloc / cudaFree / allocating library
  * call; it returns after the kernel has finished.
- * The first call on a device also looks up the address of that array and sets one
- * kernel attribute; make that first call before starting any stream capture.
+ * vsk_init does the per-device set-up for its device (it asks CUDA for the device address of that
+ * array and sets one kernel attribute, which under lazy module loading is also what makes the
+ * array and the kernel resident), so the entry point itself neither loads nor allocates; should a
+ * context reach this call without it (it cannot through vsk_init), the first call does the same
+ * set-up -- make that call before starting any stream capture.
+ * The inputs must be COMPLETE when the call is made: the library launches on its own
+ * non-blocking stream, which is not ordered after the caller's streams -- synchronise the stream
+ * (or event) that produced d_left_ids / d_top_ids first.  The ids must be 0..1000 (what
+ * vsk_profset_upload checks for host data; here they are device data the call cannot look at), and
+ * br / svector of a banded pair must be exactly what vsk_band_params returns for its lengths
+ * (checked: svector == (double)l2/l1, 7 <= br).
  * All calls on a device share the array and it keeps the previous call's contents (the
  * work counter is cleared by every call): two calls that overlap on the same GPU --
  * from two host threads or two contexts -- race; serialise them.                     */

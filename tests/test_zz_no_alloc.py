@@ -7,9 +7,10 @@ budget is fixed): inputs and outputs are device buffers the caller already owns
 (here: torch tensors), all scratch lives in a fixed array inside libvsk.so.
 
 Checked here, through the C ABI: its results equal those of the existing
-vsk_pair_dp entry point bit for bit (integer work, no tolerance), on two calls in
-a row (the shared scratch keeps the first call's contents), and oversize requests
-are refused with a message.  Collected last on purpose."""
+vsk_pair_dp entry point bit for bit (integer work, no tolerance) and those of the CPU
+oracle, on two calls in a row (the shared scratch keeps the first call's contents),
+and oversize requests or a band that vsk_band_params would not give are refused with
+a message.  Collected last on purpose."""
 import ctypes as C
 
 import numpy as np
@@ -63,7 +64,7 @@ def _run_static(ctx, profs, li, ti, mode):
     return rc, d_out.cpu().numpy()
 
 
-def test_static_matches_pair_dp_twice(ctx):
+def test_static_matches_pair_dp_twice(ctx, oracle):
     for seed, n, maxlen in ((21, 200, 300), (22, 40, 1500)):   # two calls in a row, second with wide pairs
         profs, li, ti, mode = _batch(seed, n, maxlen)
         ps = ctx.profiles(profs)
@@ -72,6 +73,8 @@ def test_static_matches_pair_dp_twice(ctx):
         rc, got = _run_static(ctx, profs, li, ti, mode)
         assert rc == 0
         assert (got == want).all()
+        for k in range(0, len(li), 7):    # and both against the CPU oracle, not only against each other
+            assert tuple(int(x) for x in got[k]) == oracle.dp(profs[li[k]], profs[ti[k]], int(mode[k]), 88), k
     # and the first batch again: nothing left over from the wide one disturbs it
     profs, li, ti, mode = _batch(21, 200, 300)
     ps = ctx.profiles(profs)
@@ -88,6 +91,18 @@ def test_static_refuses_oversize(ctx):
     rc, got = _run_static(ctx, profs, np.array([0], np.int32), np.array([1], np.int32), np.array([0], np.uint8))
     assert rc != 0 and (got == -7).all()          # refused, output untouched
     assert b"2048" in lib().vsk_last_error(ctx.h)
+    # a band that is not vsk_band_params' for these lengths is refused as well
+    from vntrseek_b200 import pack_profiles
+    import torch
+    from vntrseek_b200._lib import DpDesc
+    off, ids = pack_profiles([profs[1], profs[1]])
+    d_ids = torch.from_numpy(ids.astype(np.int16)).cuda()
+    d_out = torch.zeros((1, 4), dtype=torch.int32, device="cuda")
+    bad = (DpDesc * 1)(DpDesc(0, 50, 50, 50, 9, 0, 0.5))
+    torch.cuda.synchronize()
+    assert lib().vsk_pair_dp_static(ctx.h, d_ids.data_ptr(), len(ids), d_ids.data_ptr(), len(ids), bad, 1,
+                                    d_out.data_ptr()) != 0
+    assert b"vsk_band_params" in lib().vsk_last_error(ctx.h)
     # rows are the limit, not columns: the transposed pair is fine
     rc, got = _run_static(ctx, profs, np.array([1], np.int32), np.array([0], np.int32), np.array([0], np.uint8))
     assert rc == 0 and (got != -7).all()

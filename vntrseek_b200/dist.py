@@ -37,7 +37,7 @@ class LinkGatherer:
         self.cap = 0
         self.send = self.recv = self.host = None
         self.counts = torch.zeros(self.world, dtype=torch.int64, device=self.device)
-        self.mine = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self.phase_ms = {}
 
     def _reserve(self, mx):
         if mx <= self.cap:
@@ -54,29 +54,43 @@ class LinkGatherer:
         """links_dev: int32 tensor [n, 7] on this rank's GPU (api.DeviceLinks.tensor()).
         Returns, on the root, the merged table as a structured array in rank order (a view of the
         page-locked buffer: consume it before the next call); None on the other ranks.  With
-        to_host=False every rank gets (recv tensor [world, cap, 7], counts list) and nothing is copied."""
+        to_host=False every rank gets (recv tensor [world, cap, 7], counts list) and nothing is copied.
+        self.phase_ms accumulates host wall time per phase (counts exchange incl. the wait for the slowest
+        rank, staging copy, all-gather, host copy)."""
+        import time
         torch, dist = self.torch, self.dist
+        t0 = time.perf_counter()
         n = int(links_dev.shape[0])
-        self.mine[0] = n
-        dist.all_gather_into_tensor(self.counts, self.mine)
-        counts = [int(c) for c in self.counts.tolist()]
+        mine = torch.tensor([n], dtype=torch.int64).to(self.device, non_blocking=True)
+        dist.all_gather_into_tensor(self.counts, mine)
+        counts = [int(c) for c in self.counts.tolist()]   # waits for every rank to have arrived
+        t1 = time.perf_counter()
         self._reserve(max(max(counts), 1))
+        mx = max(max(counts), 1)
         if n:
             self.send[:n].copy_(links_dev)
-        # every rank sends `cap` records (the tail past its count is ignored by the receiver)
-        dist.all_gather_into_tensor(self.recv.view(-1), self.send.view(-1))
-        if not to_host:
-            return self.recv, counts
-        if self.rank != self.root:
-            return None
-        mx = max(counts)
-        self.host[:, :mx].copy_(self.recv[:, :mx], non_blocking=True)
+        # every rank sends `mx` records (the tail past its count is ignored by the receiver)
+        recv = self.recv.view(-1)[: self.world * mx * _NF].view(self.world, mx, _NF)
+        dist.all_gather_into_tensor(recv.view(-1), self.send[:mx].view(-1))
         if self.device.type == "cuda":
             torch.cuda.current_stream(self.device).synchronize()
-        parts = [self.host[r, :counts[r]].numpy() for r in range(self.world)]
-        if sum(counts) == 0:
-            return np.zeros(0, LINK_DTYPE)
-        return np.concatenate(parts).reshape(-1).view(LINK_DTYPE)
+        t2 = time.perf_counter()
+        self.phase_ms["counts+wait"] = self.phase_ms.get("counts+wait", 0.0) + (t1 - t0) * 1e3
+        self.phase_ms["allgather"] = self.phase_ms.get("allgather", 0.0) + (t2 - t1) * 1e3
+        if not to_host:
+            return recv, counts
+        if self.rank != self.root:
+            return None
+        host = self.host.view(-1)[: self.world * mx * _NF].view(self.world, mx, _NF)
+        for r in range(self.world):   # contiguous pieces: plain pinned copies
+            if counts[r]:
+                host[r, :counts[r]].copy_(recv[r, :counts[r]], non_blocking=True)
+        if self.device.type == "cuda":
+            torch.cuda.current_stream(self.device).synchronize()
+        parts = [host[r, :counts[r]].numpy() for r in range(self.world)]
+        out = np.concatenate(parts).reshape(-1).view(LINK_DTYPE) if sum(counts) else np.zeros(0, LINK_DTYPE)
+        self.phase_ms["host_copy"] = self.phase_ms.get("host_copy", 0.0) + (time.perf_counter() - t2) * 1e3
+        return out
 
 
 def allgather_links(links, device=None):
