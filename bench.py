@@ -42,7 +42,7 @@ import numpy as np  # noqa: E402
 
 # bytes: dram read+write of one vsk_dp_dir_kernel launch at the default workload (ncu --set full,
 # profiles/): refreshed whenever the kernel or the batch size changes
-DIR_TRAFFIC = {"bytes": 11.01e9, "source": "profiles/r01_summary.md (r01g), first 12 GiB batch of the first chunk"}
+DIR_TRAFFIC = {"bytes": 11.73e9, "source": "profiles/r02_summary.md section C (launch 0: a 12 GiB batch of the first chunk)"}
 METRIC = "proclu_read_TRs_mapped_per_sec"
 UNIT = "read-TRs/s"
 OPS_PER_CELL = 14        # algorithmic integer operations per profile-DP cell
