@@ -133,6 +133,10 @@ extern "C" void vsk_destroy(vsk_ctx *ctx) {
         if (ctx->dd_ev[i]) cudaEventDestroy(ctx->dd_ev[i]);
     for (auto &b : ctx->pin_free) cudaFreeHost(b.first);
     for (void *m : ctx->dd_mem) cudaFree(m);
+    if (ctx->h_present_pin) cudaFreeHost(ctx->h_present_pin);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->copy_go) cudaEventDestroy(ctx->copy_go);
+    if (ctx->copy_done) cudaEventDestroy(ctx->copy_done);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     delete ctx;

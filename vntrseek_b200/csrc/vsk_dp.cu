@@ -546,6 +546,121 @@ vsk_dp_tiny_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__rest
     out[job.out_idx] = make_int4((int)(lf0 & TINY_DMASK), (int)lf1, (int)(lf0 >> 22), (int)((lf0 >> 15) & 127u));
 }
 
+// ---- tiny pairs, direction-bit variant ------------------------------------------------------------
+// Same pairs as vsk_dp_tiny_kernel (<= 32 columns, <= 64 rows, full matrix), thread per pair, but like the
+// long-pair path it keeps only the distance per cell and two direction bits (bit 1: not diagonal, bit 0:
+// right rather than down; min3switch, profile.h:1098-1099), then walks the path back from the corner and
+// sums what the reference's traceback sums (profile.h:2135-2210).  About 13 instead of 30 instructions per
+// cell.  Previous row (u16: distances stay below 255 * 96) and column constants live in shared memory as
+// [column][thread]; the direction words of the <= 64 rows (two u32 per row: columns 0-15 and 16-31) in
+// the thread's local memory.
+#define TD_THREADS 128
+
+__global__ void __launch_bounds__(TD_THREADS)
+vsk_dp_tinydir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
+                      const vsk_dp_job *__restrict__ jobs, int n_jobs, const uint8_t *__restrict__ dense,
+                      const uint8_t *__restrict__ ktab, int K, const uint16_t *__restrict__ gapnd,
+                      int4 *__restrict__ out) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint16_t *s_h = reinterpret_cast<uint16_t *>(smem);                    // [33][TD_THREADS]
+    uint16_t *s_col = s_h + (TINY_MAXCOLS + 1) * TD_THREADS;               // [32][TD_THREADS]: dense index | gap << 8
+    uint16_t *s_gapnd = s_col + TINY_MAXCOLS * TD_THREADS;                 // [1024]
+    uint8_t *s_dense = reinterpret_cast<uint8_t *>(s_gapnd + 1024);        // [1024]
+    uint8_t *s_ktab = s_dense + 1024;                                      // [K*K]
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 1024; i += TD_THREADS) { s_gapnd[i] = gapnd[i]; s_dense[i] = dense[i]; }
+    for (int i = tid; i < K * K; i += TD_THREADS) s_ktab[i] = ktab[i];
+    __syncthreads();
+    const int ji = blockIdx.x * TD_THREADS + tid;
+    if (ji >= n_jobs) return;
+    const vsk_dp_job job = jobs[ji];
+    const uint16_t *L = left_ids + job.left_off;
+    const uint16_t *T = top_ids + job.top_off;
+    const int l1 = job.l1, l2 = job.l2;
+    const int n0 = min(l2, 16), n1 = l2 - n0;
+    uint32_t dirs[TINY_MAXROWS][2];
+    // row 0: cumulative gap costs (profile.h:2074-2079)
+    int acc = 0;
+    s_h[tid] = 0;
+    for (int c = 0; c < l2; ++c) {
+        const int id = T[c];
+        const int g = s_gapnd[id] & 255;
+        s_col[c * TD_THREADS + tid] = (uint16_t)(s_dense[id] | (g << 8));
+        acc += g;
+        s_h[(c + 1) * TD_THREADS + tid] = (uint16_t)acc;
+    }
+    int lf = 0;
+    for (int r = 0; r < l1; ++r) {
+        const int id = L[r];
+        const int gl = s_gapnd[id] & 255;
+        const uint8_t *krow = s_ktab + (int)s_dense[id] * K;
+        int dg = s_h[tid];
+        lf = dg + gl;  // column 0 (profile.h:2084-2090)
+        s_h[tid] = (uint16_t)lf;
+        uint32_t w0 = 0, w1 = 0;
+        for (int c = 1; c <= n0; ++c) {
+            const int cc = s_col[(c - 1) * TD_THREADS + tid];
+            const int up = s_h[c * TD_THREADS + tid];
+            const int sa = dg + krow[cc & 255], f = up + gl, e = lf + (cc >> 8);
+            const int d = min(min(sa, f), e);
+            w0 = __funnelshift_l((uint32_t)(d - sa), w0, 1);
+            w0 = __funnelshift_l((uint32_t)(e - f), w0, 1);
+            dg = up;
+            lf = d;
+            s_h[c * TD_THREADS + tid] = (uint16_t)d;
+        }
+        for (int c = n0 + 1; c <= l2; ++c) {
+            const int cc = s_col[(c - 1) * TD_THREADS + tid];
+            const int up = s_h[c * TD_THREADS + tid];
+            const int sa = dg + krow[cc & 255], f = up + gl, e = lf + (cc >> 8);
+            const int d = min(min(sa, f), e);
+            w1 = __funnelshift_l((uint32_t)(d - sa), w1, 1);
+            w1 = __funnelshift_l((uint32_t)(e - f), w1, 1);
+            dg = up;
+            lf = d;
+            s_h[c * TD_THREADS + tid] = (uint16_t)d;
+        }
+        dirs[r][0] = w0;
+        dirs[r][1] = w1;
+    }
+    // traceback from (l1, l2)
+    int r = l1, c = l2, p1 = 0, sumw = 0, len = 0;
+    while (r > 0 && c > 0) {
+        const int j = c - 1;  // column index; cell j of word 0 sits at bits 2*(n0-1-j), of word 1 at 2*(n1-1-(j-16))
+        const uint32_t bits = (j < 16) ? (dirs[r - 1][0] >> (2 * (n0 - 1 - j))) & 3u : (dirs[r - 1][1] >> (2 * (n1 - 1 - (j - 16)))) & 3u;
+        const int idl = L[r - 1], idt = T[c - 1];
+        const int gnl = s_gapnd[idl], gnt = s_gapnd[idt];
+        if (!(bits & 2u)) {
+            int dn = (gnl >> 8) + (gnt >> 8);
+            dn = dn < 10 ? dn : 10;
+            p1 += dn * (int)s_ktab[(int)s_dense[idl] * K + s_dense[idt]];
+            sumw += dn;
+            --r;
+            --c;
+        } else if (!(bits & 1u)) {
+            p1 += (gnl >> 8) * (gnl & 255);
+            sumw += gnl >> 8;
+            --r;
+        } else {
+            p1 += (gnt >> 8) * (gnt & 255);
+            sumw += gnt >> 8;
+            --c;
+        }
+        ++len;
+    }
+    for (; r > 0; --r, ++len) {  // column 0: gaps in the top profile
+        const int gnl = s_gapnd[L[r - 1]];
+        p1 += (gnl >> 8) * (gnl & 255);
+        sumw += gnl >> 8;
+    }
+    for (; c > 0; --c, ++len) {  // row 0: gaps in the left profile
+        const int gnt = s_gapnd[T[c - 1]];
+        p1 += (gnt >> 8) * (gnt & 255);
+        sumw += gnt >> 8;
+    }
+    out[job.out_idx] = make_int4(lf, p1, sumw, len);
+}
+
 __global__ void vsk_id_presence_kernel(const uint16_t *__restrict__ ids, int64_t n, uint32_t *__restrict__ out) {
     __shared__ uint32_t bm[32];
     if (threadIdx.x < 32) bm[threadIdx.x] = 0;
@@ -557,6 +672,23 @@ __global__ void vsk_id_presence_kernel(const uint16_t *__restrict__ ids, int64_t
     }
     __syncthreads();
     if (threadIdx.x < 32 && bm[threadIdx.x]) atomicOr(&out[threadIdx.x], bm[threadIdx.x]);
+}
+
+// the same on a stream of the caller's, without waiting: the bits land in ctx->h_present_pin (page-locked, so
+// that the call does not block) once the stream has got past the copy; the caller moves them to their place
+int vsk_id_presence_async(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out, cudaStream_t st) {
+    memset(out, 0, sizeof *out);
+    if (!ctx->h_present_pin) VSK_CUDA(ctx, cudaHostAlloc((void **)&ctx->h_present_pin, sizeof(out->bits), cudaHostAllocDefault));
+    memset(ctx->h_present_pin, 0, sizeof(out->bits));
+    if (n <= 0) return VSK_OK;
+    uint32_t *d = reinterpret_cast<uint32_t *>(ctx->d_queue) + 16;
+    VSK_CUDA(ctx, cudaMemsetAsync(d, 0, sizeof(out->bits), st));
+    const int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+    vsk_id_presence_kernel<<<grid, 256, 0, st>>>(d_ids, n, d);
+    ctx->launches++;
+    VSK_CUDA(ctx, cudaGetLastError());
+    VSK_CUDA(ctx, cudaMemcpyAsync(ctx->h_present_pin, d, sizeof(out->bits), cudaMemcpyDeviceToHost, st));
+    return VSK_OK;
 }
 
 int vsk_id_presence(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out) {
@@ -699,7 +831,24 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         ctx->launches++;
         VSK_CUDA(ctx, cudaGetLastError());
     }
-    if (n_tiny > 0) {
+    static const bool use_tinydir = [] {
+        const char *e = getenv("VSK_DP_TINYDIR");
+        return !(e && e[0] == '0');
+    }();
+    if (n_tiny > 0 && use_tinydir) {
+        const size_t smem = (size_t)(2 * TINY_MAXCOLS + 1) * TD_THREADS * 2 + 2048 + 1024 + (size_t)K * K;
+        static uint64_t attr_td = 0;
+        if (!((attr_td >> (ctx->device & 63)) & 1)) {
+            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_tinydir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)((2 * TINY_MAXCOLS + 1) * TD_THREADS * 2 + 2048 + 1024 + 200 * 200)));
+            attr_td |= 1ull << (ctx->device & 63);
+        }
+        vsk_dp_tinydir_kernel<<<(unsigned)((n_tiny + TD_THREADS - 1) / TD_THREADS), TD_THREADS, smem, ctx->stream>>>(
+            d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,
+            ctx->d_gapnd, d_out);
+        ctx->launches++;
+        VSK_CUDA(ctx, cudaGetLastError());
+    } else if (n_tiny > 0) {
         const size_t smem = (size_t)(2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 + 2048 + 1024 +
                             (size_t)K * K;
         if (!((g_tiny_attr_set >> (ctx->device & 63)) & 1)) {

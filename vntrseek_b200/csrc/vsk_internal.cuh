@@ -28,6 +28,11 @@ struct vsk_ctx {
     // stream-ordered allocations come from a pool of this context (freed memory stays in it between
     // runs); the device's default pool, which a host application may use itself, is left alone
     cudaMemPool_t pool = nullptr;
+    // copy stream of vsk_proclu_run: the composition ids and flanks of a read set travel on it while the first
+    // stages of the scan already run (copy_go: buffers allocated; copy_done: data and presence bits arrived)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t copy_go = nullptr, copy_done = nullptr;
+    uint32_t *h_present_pin = nullptr;  // page-locked landing place of the presence bits computed on the copy stream
     uint8_t *d_dist = nullptr;    // [VSK_NIDS][VSK_DROW] symmetric distances
     uint16_t *d_gapnd = nullptr;  // [1024]: d(0,id) | NONDASHES[id] << 8
     uint8_t h_nd[VSK_NIDS];
@@ -139,6 +144,7 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
 int vsk_dp_static_setup(vsk_ctx *ctx);
 // which composition ids occur in d_ids[0..n)
 int vsk_id_presence(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out);
+int vsk_id_presence_async(vsk_ctx *ctx, const uint16_t *d_ids, int64_t n, vsk_idset *out, cudaStream_t st);
 
 int vsk_lcs_launch(vsk_ctx *ctx, const uint8_t *d_seqA, const int64_t *d_offA, const uint8_t *d_seqB,
                    const int64_t *d_offB, const int32_t *d_ia, const int32_t *d_ib, int64_t n,

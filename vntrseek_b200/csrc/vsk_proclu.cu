@@ -71,6 +71,9 @@ struct vsk_reads {
     int64_t h2d_bytes = 0;
     vsk_idset present;  // composition ids that occur in this set
     mutable bool checked = false;  // the pattern-size / tuple-size checks passed (done once per upload)
+    // the composition ids and the flanks (what the scan needs last: profile DP, flank test) may still be on
+    // their way on the context's copy stream while the seed / LCS stages run; ctx->copy_done marks their arrival
+    mutable bool deferred = false;
 };
 
 struct vsk_refs {
@@ -339,7 +342,7 @@ static int decode_raw_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads *r) {
     return vsk_trset_check_limits(ctx, ts);  // the consensus lengths are known now
 }
 
-static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
+static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out, bool defer_big = false) {
     *out = nullptr;
     if (int lim = vsk_trset_check_limits(ctx, ts)) return lim;
     vsk_reads *r = new vsk_reads();
@@ -366,8 +369,31 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
     if (ts->raw) {
         if ((rc = decode_raw_trset(ctx, ts, r))) { *out = r; return rc; }
     } else {
-        UP(prof_off, ts->prof_off) UP(cons_off, ts->cons_off) UP(fl_off, ts->fl_off) UP(ids, ts->ids)
-        UPB(cons, ts->cons) UPB(fl, ts->fl)
+        UP(prof_off, ts->prof_off) UP(cons_off, ts->cons_off) UP(fl_off, ts->fl_off)
+        UPB(cons, ts->cons)
+        if (!defer_big) {
+            UP(ids, ts->ids) UPB(fl, ts->fl)
+        } else {
+            // ids and flanks: allocated in stream order here, copied on the copy stream, so that the copy (the
+            // larger half of the set) overlaps the seed and LCS stages, which read neither
+            if (!ctx->copy_stream) VSK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+            if (!ctx->copy_done) VSK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->copy_done, cudaEventDisableTiming));
+            if (!ctx->copy_go) VSK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->copy_go, cudaEventDisableTiming));
+            VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)&r->d.ids, sizeof(uint16_t) * (ts->ids.size() + 8), ctx->pool, ctx->stream));
+            r->allocs.push_back(r->d.ids);
+            VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)&r->d.fl, ts->fl.size() + 64, ctx->pool, ctx->stream));
+            r->allocs.push_back(r->d.fl);
+            VSK_CUDA(ctx, cudaEventRecord(ctx->copy_go, ctx->stream));
+            VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->copy_go, 0));
+            r->deferred = true;  // from here on the copy stream owns the two buffers until copy_done
+            if (!ts->ids.empty())
+                VSK_CUDA(ctx, cudaMemcpyAsync(r->d.ids, ts->ids.data(), sizeof(uint16_t) * ts->ids.size(), cudaMemcpyHostToDevice, ctx->copy_stream));
+            if (!ts->fl.empty())
+                VSK_CUDA(ctx, cudaMemcpyAsync(r->d.fl, ts->fl.data(), ts->fl.size(), cudaMemcpyHostToDevice, ctx->copy_stream));
+            r->h2d_bytes += (int64_t)(sizeof(uint16_t) * ts->ids.size() + ts->fl.size());
+            if ((rc = vsk_id_presence_async(ctx, r->d.ids, ts->prof_off.back(), &r->present, ctx->copy_stream))) { *out = r; return rc; }
+            VSK_CUDA(ctx, cudaEventRecord(ctx->copy_done, ctx->copy_stream));
+        }
     }
     UP(leftlen, ts->leftlen) UP(rightlen, ts->rightlen) UP(patlen, ts->patlen)
     UP(key, ts->key) UP(rot_off, ts->rot_off) UP(rot_mem, ts->rot_mem) UP(dir, ts->dir) UP(master, ts->master)
@@ -393,11 +419,23 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out) {
     }
     VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     *out = r;
+    if (r->deferred) return VSK_OK;  // the presence bits arrive with copy_done
     return vsk_id_presence(ctx, r->d.ids, ts->prof_off.back(), &r->present);
+}
+
+// the scan is about to touch the composition ids / flanks (or the set is going away): wait for their copy
+static int reads_arrived(vsk_ctx *ctx, const vsk_reads *r) {
+    if (r && r->deferred) {
+        VSK_CUDA(ctx, cudaEventSynchronize(ctx->copy_done));
+        memcpy(const_cast<vsk_reads *>(r)->present.bits, ctx->h_present_pin, sizeof(r->present.bits));
+        r->deferred = false;
+    }
+    return VSK_OK;
 }
 
 static void free_reads(vsk_reads *r) {
     if (!r) return;
+    if (r->deferred) cudaEventSynchronize(r->ctx->copy_done);
     for (void *p : r->allocs) cudaFreeAsync(p, r->ctx->stream);
     delete r;
 }
@@ -1342,9 +1380,11 @@ static int run_chunk(vsk_ctx *ctx, const vsk_refs *R, const vsk_reads *Q, const 
     vsk_gather_jobs_kernel<<<blocks(ndp, 256), 256, 0, st>>>(jobs, order2, ndp, sorted);
     ctx->launches++;
     vsk_stage_mark(ctx, "dp_schedule");
+    int rc = reads_arrived(ctx, Q);  // ids, flanks and the presence bits of a set still in flight
+    if (rc) return rc;
     vsk_idset ids;
     for (int k = 0; k < 32; ++k) ids.bits[k] = R->tr->present.bits[k] | Q->present.bits[k];
-    int rc = vsk_dp_launch(ctx, refs.ids, reads.ids, sorted, ndp, (int64_t)hs[8], (int64_t)hs[7], (int32_t)hs[2], &ids, res);
+    rc = vsk_dp_launch(ctx, refs.ids, reads.ids, sorted, ndp, (int64_t)hs[8], (int64_t)hs[7], (int32_t)hs[2], &ids, res);
     if (rc) return rc;
     vsk_stage_mark(ctx, "dp_kernel");
     // similarity test + flank expansion
@@ -1533,8 +1573,9 @@ extern "C" int vsk_proclu_run(vsk_ctx *ctx, const vsk_refs *R, const vsk_trset *
                               vsk_proclu_result **out) {
     if (!ctx || !R || !reads || !out) return VSK_ERR_ARG;
     vsk_reads *Q = nullptr;
-    int rc = vsk_reads_upload(ctx, reads, &Q);
-    if (rc) return rc;
+    VSK_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = upload_trset(ctx, reads, &Q, /*defer_big=*/!reads->raw);
+    if (rc) { free_reads(Q); return rc; }
     const int64_t h2d = Q->h2d_bytes;
     rc = vsk_proclu_run_resident(ctx, R, Q, prm, out);
     if (rc == VSK_OK) (*out)->stats.h2d_bytes = h2d;
