@@ -18,7 +18,7 @@ def _segments(L):
     return off
 
 
-def _dp_pairs(seed, n_small, n_mid, n_big):
+def _dp_pairs(seed, n_small, n_mid, n_big, wide=True):
     """left/top profile sets + pair list: mutated copies, ratio extremes, unrelated pairs"""
     from vntrseek_b200 import synth
     rng = np.random.default_rng(seed)
@@ -31,8 +31,9 @@ def _dp_pairs(seed, n_small, n_mid, n_big):
     n = len(L)
     loff, lids = synth._random_profiles(rng, L)
     lids = lids.astype(np.uint16)
-    anyid = rng.random(len(lids)) < 0.02          # a few columns from the whole alphabet
-    lids[anyid] = rng.integers(0, 1001, int(anyid.sum()))
+    if wide:   # a few columns from the whole alphabet: more than 200 distinct compositions in the data set
+        anyid = rng.random(len(lids)) < 0.02
+        lids[anyid] = rng.integers(0, 1001, int(anyid.sum()))
     # top profiles: 55 % mutated copies, 25 % random of a length in [L/2, 2L], 20 % unrelated lengths
     kind = rng.random(n)
     mut, moff = synth._mutate_segments(rng, lids.astype(np.int32), loff, 0.05, 0.03,
@@ -60,8 +61,12 @@ def _dp_pairs(seed, n_small, n_mid, n_big):
     return (loff, lids), (toff, tids), li2, ti2, mode
 
 
-def test_dp_million_pairs_vs_oracle(ctx, oracle):
-    (loff, lids), (toff, tids), li, ti, mode = _dp_pairs(101, 600000, 3000, 120)
+@pytest.mark.parametrize("wide", [False, True])
+def test_dp_million_pairs_vs_oracle(ctx, oracle, wide):
+    """wide=False: the data set uses 56 compositions, the small-pair kernels take their costs from the dense
+    K x K table in shared memory; wide=True: all 1001 occur, they read the global table"""
+    (loff, lids), (toff, tids), li, ti, mode = _dp_pairs(101 + int(wide), 600000, 3000, 120, wide)
+    assert (len(np.unique(lids)) > 200) == wide
     assert len(li) >= 1000000
     left = ctx.profiles(off=loff, ids=lids)
     top = ctx.profiles(off=toff, ids=tids)

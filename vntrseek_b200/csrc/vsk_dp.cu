@@ -556,20 +556,26 @@ vsk_dp_tiny_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__rest
 // the thread's local memory.
 #define TD_THREADS 128
 
+// DENSE: costs from the K x K table of the data set's compositions in shared memory; otherwise (more than 200
+// distinct compositions) the column constant is the id itself and costs come from the global table.
+template <bool DENSE>
 __global__ void __launch_bounds__(TD_THREADS)
 vsk_dp_tinydir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
                       const vsk_dp_job *__restrict__ jobs, int n_jobs, const uint8_t *__restrict__ dense,
-                      const uint8_t *__restrict__ ktab, int K, const uint16_t *__restrict__ gapnd,
-                      int4 *__restrict__ out) {
+                      const uint8_t *__restrict__ ktab, int K, const uint8_t *__restrict__ dist,
+                      const uint16_t *__restrict__ gapnd, int4 *__restrict__ out) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint16_t *s_h = reinterpret_cast<uint16_t *>(smem);                    // [33][TD_THREADS]
-    uint16_t *s_col = s_h + (TINY_MAXCOLS + 1) * TD_THREADS;               // [32][TD_THREADS]: dense index | gap << 8
+    uint16_t *s_col = s_h + (TINY_MAXCOLS + 1) * TD_THREADS;               // [32][TD_THREADS]: dense index | gap << 8 (DENSE), else the id
     uint16_t *s_gapnd = s_col + TINY_MAXCOLS * TD_THREADS;                 // [1024]
     uint8_t *s_dense = reinterpret_cast<uint8_t *>(s_gapnd + 1024);        // [1024]
     uint8_t *s_ktab = s_dense + 1024;                                      // [K*K]
     const int tid = threadIdx.x;
-    for (int i = tid; i < 1024; i += TD_THREADS) { s_gapnd[i] = gapnd[i]; s_dense[i] = dense[i]; }
-    for (int i = tid; i < K * K; i += TD_THREADS) s_ktab[i] = ktab[i];
+    for (int i = tid; i < 1024; i += TD_THREADS) s_gapnd[i] = gapnd[i];
+    if (DENSE) {
+        for (int i = tid; i < 1024; i += TD_THREADS) s_dense[i] = dense[i];
+        for (int i = tid; i < K * K; i += TD_THREADS) s_ktab[i] = ktab[i];
+    }
     __syncthreads();
     const int ji = blockIdx.x * TD_THREADS + tid;
     if (ji >= n_jobs) return;
@@ -585,7 +591,7 @@ vsk_dp_tinydir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__r
     for (int c = 0; c < l2; ++c) {
         const int id = T[c];
         const int g = s_gapnd[id] & 255;
-        s_col[c * TD_THREADS + tid] = (uint16_t)(s_dense[id] | (g << 8));
+        s_col[c * TD_THREADS + tid] = DENSE ? (uint16_t)(s_dense[id] | (g << 8)) : (uint16_t)id;
         acc += g;
         s_h[(c + 1) * TD_THREADS + tid] = (uint16_t)acc;
     }
@@ -593,7 +599,7 @@ vsk_dp_tinydir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__r
     for (int r = 0; r < l1; ++r) {
         const int id = L[r];
         const int gl = s_gapnd[id] & 255;
-        const uint8_t *krow = s_ktab + (int)s_dense[id] * K;
+        const uint8_t *krow = DENSE ? (s_ktab + (int)s_dense[id] * K) : (dist + id * VSK_DROW);
         int dg = s_h[tid];
         lf = dg + gl;  // column 0 (profile.h:2084-2090)
         s_h[tid] = (uint16_t)lf;
@@ -601,7 +607,8 @@ vsk_dp_tinydir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__r
         for (int c = 1; c <= n0; ++c) {
             const int cc = s_col[(c - 1) * TD_THREADS + tid];
             const int up = s_h[c * TD_THREADS + tid];
-            const int sa = dg + krow[cc & 255], f = up + gl, e = lf + (cc >> 8);
+            const int sa = dg + (DENSE ? (int)krow[cc & 255] : (int)__ldg(krow + cc)), f = up + gl;
+            const int e = lf + (DENSE ? (cc >> 8) : (int)(s_gapnd[cc] & 255));
             const int d = min(min(sa, f), e);
             w0 = __funnelshift_l((uint32_t)(d - sa), w0, 1);
             w0 = __funnelshift_l((uint32_t)(e - f), w0, 1);
@@ -612,7 +619,8 @@ vsk_dp_tinydir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__r
         for (int c = n0 + 1; c <= l2; ++c) {
             const int cc = s_col[(c - 1) * TD_THREADS + tid];
             const int up = s_h[c * TD_THREADS + tid];
-            const int sa = dg + krow[cc & 255], f = up + gl, e = lf + (cc >> 8);
+            const int sa = dg + (DENSE ? (int)krow[cc & 255] : (int)__ldg(krow + cc)), f = up + gl;
+            const int e = lf + (DENSE ? (cc >> 8) : (int)(s_gapnd[cc] & 255));
             const int d = min(min(sa, f), e);
             w1 = __funnelshift_l((uint32_t)(d - sa), w1, 1);
             w1 = __funnelshift_l((uint32_t)(e - f), w1, 1);
@@ -633,7 +641,7 @@ vsk_dp_tinydir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__r
         if (!(bits & 2u)) {
             int dn = (gnl >> 8) + (gnt >> 8);
             dn = dn < 10 ? dn : 10;
-            p1 += dn * (int)s_ktab[(int)s_dense[idl] * K + s_dense[idt]];
+            p1 += dn * (DENSE ? (int)s_ktab[(int)s_dense[idl] * K + s_dense[idt]] : (int)__ldg(dist + idl * VSK_DROW + idt));
             sumw += dn;
             --r;
             --c;
@@ -754,14 +762,6 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         int rc = tiny_tables(ctx, ids, &K);
         if (rc) return rc;
     }
-    if (K == 0) n_tiny = n_q8 = 0;  // no dense table: everything goes through the warp-per-pair kernel
-    const int64_t n_warp = n_jobs - n_tiny - n_q8;
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (ctx->profile) {
-        VSK_CUDA(ctx, cudaEventCreate(&e0));
-        VSK_CUDA(ctx, cudaEventCreate(&e1));
-        VSK_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
-    }
     static const bool use_dir = [] {
         const char *e = getenv("VSK_DP_DIR");
         return !(e && e[0] == '0');
@@ -770,6 +770,21 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         const char *e = getenv("VSK_DP_DIRQ8");
         return !(e && e[0] == '0');
     }();
+    static const bool use_tinydir = [] {
+        const char *e = getenv("VSK_DP_TINYDIR");
+        return !(e && e[0] == '0');
+    }();
+    // K == 0: the data set uses more than 200 distinct compositions (no dense table).  The direction-bit small-pair
+    // kernels then read the global table; the older sum-carrying kernels (run-time switches) need the dense table,
+    // so with one of them selected everything goes through the warp-per-pair kernels.
+    if (K == 0 && (!use_tinydir || !(use_dir && use_dir_q8))) n_tiny = n_q8 = 0;
+    const int64_t n_warp = n_jobs - n_tiny - n_q8;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ctx->profile) {
+        VSK_CUDA(ctx, cudaEventCreate(&e0));
+        VSK_CUDA(ctx, cudaEventCreate(&e1));
+        VSK_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+    }
     const bool dir_q8 = use_dir && use_dir_q8 && n_q8 > 0;  // the 8-lane jobs take the direction-bit path too
     const bool dir_any = use_dir && (n_warp > 0 || dir_q8);
     int64_t grid_w = 0;
@@ -831,21 +846,23 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         ctx->launches++;
         VSK_CUDA(ctx, cudaGetLastError());
     }
-    static const bool use_tinydir = [] {
-        const char *e = getenv("VSK_DP_TINYDIR");
-        return !(e && e[0] == '0');
-    }();
     if (n_tiny > 0 && use_tinydir) {
         const size_t smem = (size_t)(2 * TINY_MAXCOLS + 1) * TD_THREADS * 2 + 2048 + 1024 + (size_t)K * K;
         static uint64_t attr_td = 0;
         if (!((attr_td >> (ctx->device & 63)) & 1)) {
-            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_tinydir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_tinydir_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                (int)((2 * TINY_MAXCOLS + 1) * TD_THREADS * 2 + 2048 + 1024 + 200 * 200)));
             attr_td |= 1ull << (ctx->device & 63);
         }
-        vsk_dp_tinydir_kernel<<<(unsigned)((n_tiny + TD_THREADS - 1) / TD_THREADS), TD_THREADS, smem, ctx->stream>>>(
-            d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,
-            ctx->d_gapnd, d_out);
+        const unsigned gridt = (unsigned)((n_tiny + TD_THREADS - 1) / TD_THREADS);
+        if (K > 0)
+            vsk_dp_tinydir_kernel<true><<<gridt, TD_THREADS, smem, ctx->stream>>>(
+                d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,
+                ctx->d_dist, ctx->d_gapnd, d_out);
+        else
+            vsk_dp_tinydir_kernel<false><<<gridt, TD_THREADS, smem, ctx->stream>>>(
+                d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, nullptr, nullptr, 0, ctx->d_dist,
+                ctx->d_gapnd, d_out);
         ctx->launches++;
         VSK_CUDA(ctx, cudaGetLastError());
     } else if (n_tiny > 0) {

@@ -409,10 +409,13 @@ vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restr
 
 __host__ __device__ inline int dq_cpl(int l2) { return l2 <= 32 ? 4 : l2 <= 64 ? 8 : 16; }
 
-template <int CPL>
+// DENSE: costs from the K x K table of the data set's compositions in shared memory; otherwise (more than 200
+// distinct compositions in the data set) from the symmetric table in global memory.
+template <int CPL, bool DENSE>
 __device__ __forceinline__ void dq_pair(const vsk_dp_job &job, const uint16_t *__restrict__ L,
                                         const uint16_t *__restrict__ Tp, const uint16_t *s_gapnd,
-                                        const uint8_t *s_dense, const uint8_t *s_ktab, int K, uint32_t *ring,
+                                        const uint8_t *s_dense, const uint8_t *s_ktab, int K,
+                                        const uint8_t *__restrict__ dist, uint32_t *ring,
                                         unsigned gmask, int glane, uint32_t *__restrict__ dir, int4 *out) {
     const int l1 = job.l1, l2 = job.l2, br = job.br;
     const bool banded = br >= 0;
@@ -424,7 +427,7 @@ __device__ __forceinline__ void dq_pair(const vsk_dp_job &job, const uint16_t *_
         const int c = cbase + j;
         const int id = (c < l2) ? (int)Tp[c] : 0;
         gt[j] = s_gapnd[id] & 255;
-        tb[j] = s_dense[id];
+        tb[j] = DENSE ? (int)s_dense[id] : id;
         sd += gt[j];
         Hd[j] = sd;
     }
@@ -453,10 +456,10 @@ __device__ __forceinline__ void dq_pair(const vsk_dp_job &job, const uint16_t *_
         const int id = id_next;
         id_next = L[min(max(r + 1, 0), l1 - 1)];
         const int gl = s_gapnd[id] & 255;
-        const uint8_t *trow = s_ktab + (int)s_dense[id] * K;
+        const uint8_t *trow = DENSE ? (s_ktab + (int)s_dense[id] * K) : (dist + id * VSK_DROW);
         if (active) {
             if (glane == 0) lfd = dgd + gl;  // column 0, profile.h:2084-2090
-            const uint32_t w = dd_row_cells<CPL, true>(Hd, Hd, tb, gt, dgd, lfd, trow, gl);
+            const uint32_t w = dd_row_cells<CPL, DENSE>(Hd, Hd, tb, gt, dgd, lfd, trow, gl);
             dgd = lfd;
             ring[r & 15] = w;
         }
@@ -498,19 +501,24 @@ __device__ __forceinline__ void dq_pair(const vsk_dp_job &job, const uint16_t *_
 }
 
 // jobs[q_begin..q_end) are the 8-lane jobs; a batch takes the part of its range that lies in there
+template <bool DENSE>
 __global__ void __launch_bounds__(DQ_WARPS * 32)
 vsk_dp_q8dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restrict__ top_ids,
                     const vsk_dp_job *__restrict__ jobs, const int64_t *__restrict__ dir_off,
                     const int *__restrict__ bounds, int batch, int64_t batch_words, int q_begin, int q_end,
                     const uint8_t *__restrict__ dense, const uint8_t *__restrict__ ktab, int K,
-                    const uint16_t *__restrict__ gapnd, uint32_t *__restrict__ dirbuf, int *queue, int4 *out) {
+                    const uint8_t *__restrict__ dist, const uint16_t *__restrict__ gapnd,
+                    uint32_t *__restrict__ dirbuf, int *queue, int4 *out) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint16_t *s_gapnd = reinterpret_cast<uint16_t *>(smem);
     uint32_t *s_ring = reinterpret_cast<uint32_t *>(smem + 2048);  // [thread][16]
     uint8_t *s_dense = smem + 2048 + DQ_WARPS * 32 * 64;
     uint8_t *s_ktab = s_dense + 1024;
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) { s_gapnd[i] = gapnd[i]; s_dense[i] = dense[i]; }
-    for (int i = threadIdx.x; i < K * K; i += blockDim.x) s_ktab[i] = ktab[i];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_gapnd[i] = gapnd[i];
+    if (DENSE) {
+        for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_dense[i] = dense[i];
+        for (int i = threadIdx.x; i < K * K; i += blockDim.x) s_ktab[i] = ktab[i];
+    }
     __syncthreads();
     const int lane = threadIdx.x & 31, glane = lane & (DQ_G - 1);
     const unsigned gmask = 0xffu << (lane & ~(DQ_G - 1));
@@ -525,9 +533,9 @@ vsk_dp_q8dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
         const uint16_t *L = left_ids + job.left_off;
         const uint16_t *Tp = top_ids + job.top_off;
         uint32_t *dir = dirbuf + (dir_off[ji] - (int64_t)batch * batch_words);
-        if (job.l2 <= 32) dq_pair<4>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, ring, gmask, glane, dir, out);
-        else if (job.l2 <= 64) dq_pair<8>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, ring, gmask, glane, dir, out);
-        else dq_pair<16>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, ring, gmask, glane, dir, out);
+        if (job.l2 <= 32) dq_pair<4, DENSE>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, dist, ring, gmask, glane, dir, out);
+        else if (job.l2 <= 64) dq_pair<8, DENSE>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, dist, ring, gmask, glane, dir, out);
+        else dq_pair<16, DENSE>(job, L, Tp, s_gapnd, s_dense, s_ktab, K, dist, ring, gmask, glane, dir, out);
         __syncwarp(gmask);
     }
 }
@@ -783,17 +791,21 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     if (per_sm < 1) per_sm = 1;
     const int grid = ctx->sm_count * per_sm;
     // the 8-lane kernel
+    const bool dense = K > 0;  // K == 0: no dense table for this data set, the 8-lane kernel reads the global table
     const size_t dq_smem = 2048 + DQ_WARPS * 32 * 64 + 1024 + (size_t)K * K;
     int grid8 = 0;
     if (n_q8 > 0) {
         static uint64_t attr8 = 0;
         if (!((attr8 >> (ctx->device & 63)) & 1)) {
-            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_q8dir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_q8dir_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                2048 + DQ_WARPS * 32 * 64 + 1024 + 200 * 200));
             attr8 |= 1ull << (ctx->device & 63);
         }
         int per_sm8 = 0;
-        VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm8, vsk_dp_q8dir_kernel, DQ_WARPS * 32, dq_smem));
+        if (dense)
+            VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm8, vsk_dp_q8dir_kernel<true>, DQ_WARPS * 32, dq_smem));
+        else
+            VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm8, vsk_dp_q8dir_kernel<false>, DQ_WARPS * 32, dq_smem));
         grid8 = ctx->sm_count * (per_sm8 < 1 ? 1 : per_sm8);
     }
     const int stride = ((max_l1 + 31) / 32) * 32 + 128;  // slack: the steady phase fetches up to 96 rows past the last
@@ -836,9 +848,14 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
             }
         }
         if (n_q8 > 0 && b >= h_q8_first) {
-            vsk_dp_q8dir_kernel<<<grid8, DQ_WARPS * 32, dq_smem, st>>>(
-                d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b, batch_words, (int)n_warp, (int)n, ctx->d_tiny_dense,
-                ctx->d_tiny_ktab, K, ctx->d_gapnd, dir, d_queue8 + b, d_out);
+            if (dense)
+                vsk_dp_q8dir_kernel<true><<<grid8, DQ_WARPS * 32, dq_smem, st>>>(
+                    d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b, batch_words, (int)n_warp, (int)n,
+                    ctx->d_tiny_dense, ctx->d_tiny_ktab, K, ctx->d_dist, ctx->d_gapnd, dir, d_queue8 + b, d_out);
+            else
+                vsk_dp_q8dir_kernel<false><<<grid8, DQ_WARPS * 32, dq_smem, st>>>(
+                    d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b, batch_words, (int)n_warp, (int)n, nullptr,
+                    nullptr, 0, ctx->d_dist, ctx->d_gapnd, dir, d_queue8 + b, d_out);
             ctx->launches++;
         }
         vsk_dp_trace_kernel<<<ctx->sm_count * 16, DT_THREADS, 0, st>>>(d_left_ids, d_top_ids, d_jobs, d_off, d_bounds, b,
