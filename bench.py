@@ -84,11 +84,13 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, dev):
+    def __init__(self, dev, period_ms=200):
         self.p = None
+        if period_ms <= 0:
+            return
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(dev), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", "200"],
+                                       "--format=csv,noheader,nounits", "-lms", str(int(period_ms))],
                                       stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             pass
@@ -343,6 +345,9 @@ def ours(args, rank, world, local_rank):
 
     def barrier():
         if world > 1:
+            if pending[0] is not None:  # the merged table of the last step is on the host before the clock stops
+                pending[0].wait()
+                pending[0] = None
             dist.barrier()
         torch.cuda.synchronize()
         ctx.sync()
@@ -353,6 +358,7 @@ def ours(args, rank, world, local_rank):
         gatherer = LinkGatherer("cuda:%d" % local_rank, root=0)
     ag_ev = [torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)] if world > 1 else None
     ag_ms = [0.0]
+    pending = [None]
 
     def step(reads_arg, timed):
         """one pass; N > 1: the links stay in HBM and go straight into the all-gather, the root
@@ -363,7 +369,9 @@ def ours(args, rank, world, local_rank):
         dl, st = v.proclu(ctx, idx, reads_arg, links_on_device=True)
         if timed:
             ag_ev[0].record()
-        gatherer.gather(dl.tensor())
+        if pending[0] is not None:
+            pending[0].wait()           # the root's copy of the previous step's table (it overlapped this scan)
+        pending[0] = gatherer.gather(dl.tensor())
         if timed:
             ag_ev[1].record()
             ag_ev[1].synchronize()
@@ -377,7 +385,7 @@ def ours(args, rank, world, local_rank):
     for _ in range(W):
         stats = step(resident, False)
     barrier()
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, args.clock_ms)
     ctx.profile(True)
     l0 = ctx.launches
     ctx.timer_start()
@@ -435,6 +443,8 @@ def ours(args, rank, world, local_rank):
     rank_ag_ms = allgather_floats(ag_resident_ms)
     rank_scan_ms = allgather_floats(sum(stages.values()) / K)
     rank_cells = allgather_floats(float(stats_cells["dp_cells"]))
+    rank_dp_ms = allgather_floats(dp_ms / K)
+    rank_sm_mhz = allgather_floats(float(clocks.get("sm_mhz") or 0.0))
     step_ms = allmax(max(dev_ms, wall_ms)) / K
     e2e_step_ms = allmax(e2e_ms) / K
     total_reads = allsum(float(len(reads)))
@@ -527,6 +537,7 @@ def ours(args, rank, world, local_rank):
                                       "rank waits for the slowest rank's scan to finish (per_rank below)")
             line["per_rank"] = {"ms_per_step": rank_step_ms, "scan_ms_per_step": rank_scan_ms,
                                 "allgather_ms_per_step": rank_ag_ms, "dp_cells_per_step": rank_cells,
+                                "dp_stage_ms_per_step": rank_dp_ms, "sm_mhz": rank_sm_mhz,
                                 "rank0_merge_phases_host_ms": ag_phases}
         if parity is not None:
             line["parity_at_scale"] = parity
@@ -871,6 +882,7 @@ def main():
     ap.add_argument("--flank-pairs", type=int, default=50000000)
     ap.add_argument("--flank-cpu-pairs", type=int, default=1000000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--clock-ms", type=int, default=200, help="nvidia-smi sampling period during the timed region (0 = off)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

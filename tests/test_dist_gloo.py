@@ -61,7 +61,7 @@ def _worker_gatherer(rank, world, port, n, outdir):
         got = g.gather(t)
         assert (got is None) == (rank != 0)
         if rank == 0:
-            np.save(os.path.join(outdir, "g%d.npy" % rep), got)
+            np.save(os.path.join(outdir, "g%d.npy" % rep), got.wait())
     recv, counts = g.gather(t, to_host=False)
     assert sum(counts) == n and recv.shape[0] == world
     dist.destroy_process_group()

@@ -142,18 +142,27 @@ __device__ __forceinline__ uint32_t dd_row_cells(const int (&Hin)[CPL], int (&Ho
                                                  const int (&gt)[CPL], int dgd, int lfd,
                                                  const uint8_t *__restrict__ trow, int gl) {
     uint32_t w = 0;
+    const uint32_t sbase = SMEMT ? (uint32_t)__cvta_generic_to_shared(trow) : 0u;
 #pragma unroll
     for (int j = 0; j < CPL; ++j) {
         const int upd = Hin[j];
-        const int dlt = SMEMT ? (int)trow[tb[j]] : (int)__ldg(trow + tb[j]);
-        const int sa = dgd + dlt;   // diagonal
-        const int f = upd + gl;     // down
-        const int e = lfd + gt[j];  // right
+        int dlt;
+        if (SMEMT) {
+            // the table address as a multiply-add: it issues on the FMA pipe, the ALU pipe is the busier one
+            uint32_t a;
+            asm("mad.lo.u32 %0, %1, 1, %2;" : "=r"(a) : "r"(tb[j]), "r"(sbase));
+            asm("ld.shared.u8 %0, [%1];" : "=r"(dlt) : "r"(a));
+        } else {
+            dlt = (int)__ldg(trow + tb[j]);
+        }
+        const int sa = dgd + dlt;                     // diagonal
+        const int t = __viaddmin_s32(upd, gl, sa);    // min(down, diagonal)
+        const int d = __viaddmin_s32(lfd, gt[j], t);  // min(right, t)
         // min3switch (profile.h:1098-1099): diag if sa<=f && sa<=e; else down if f<=e; else right.
-        // d = min3, so "not diagonal" is the sign of d - sa and "right" is the sign of e - f.
-        const int d = min(min(sa, f), e);
-        w = __funnelshift_l((uint32_t)(d - sa), w, 1);
-        w = __funnelshift_l((uint32_t)(e - f), w, 1);
+        // With t = min(f, sa): right iff e < t (then e < sa and e < f); otherwise down iff f < sa (then
+        // f <= e), otherwise diagonal.  Bit 1 = sign of t - sa (f < sa), bit 0 = sign of d - t (e < t).
+        w = __funnelshift_l((uint32_t)(t - sa), w, 1);
+        w = __funnelshift_l((uint32_t)(d - t), w, 1);
         dgd = upd;
         Hout[j] = d;
         lfd = d;
@@ -249,7 +258,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             const bool active = (r >= r_lo) && (r < r_hi);
             const uint32_t rec = rec_next;
             rec_next = __ldcg(rowrec + min(max(r + 1, 0), l1 - 1));
-            const int gl = (int)(rec >> 16);
+            const int gl = (int)__byte_perm(rec, 0u, 0x4432);  // rec >> 16, kept out of the per-cell adds
             const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
             if (active) {
                 if (lane == 0) {
@@ -307,7 +316,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                     int lfd = __shfl_up_sync(DD_FULL, Hin[CPL - 1], 1);
                     const uint32_t rec = rec_next;
                     rec_next = ws.win[(r + 1) & 63];
-                    const int gl = (int)(rec >> 16);
+                    const int gl = (int)__byte_perm(rec, 0u, 0x4432);  // rec >> 16, kept out of the per-cell adds
                     const uint8_t *trow = SMEMT ? (ws.T + (rec & 0xffffu)) : (dist + (rec & 0xffffu) * VSK_DROW);
                     const int v = __shfl_sync(DD_FULL, bcur, k & 31);  // previous strip's last cell of row s+1
                     if (lane == 0) lfd = first ? dgd + gl : nxt;       // column 0 (profile.h:2084-2090) : boundary
@@ -617,18 +626,18 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
                 wr = r;
                 wl = sl;
             }
-            const uint32_t bits = (w >> (2 * (cpl - 1 - j))) & 3u;  // bit 1: not diagonal, bit 0: right
+            const uint32_t bits = (w >> (2 * (cpl - 1 - j))) & 3u;  // bit 0: right; else bit 1: down; else diagonal
             const int idl = L[r - 1], idt = Tp[c - 1];
             const int gnl = s_gapnd[idl], gnt = s_gapnd[idt];
             bool left = false;
-            if (!(bits & 2u)) {
+            if (bits == 0u) {
                 int dn = (gnl >> 8) + (gnt >> 8);
                 dn = dn < 10 ? dn : 10;
                 p1 += dn * (int)__ldg(dist + idl * VSK_DROW + idt);
                 sumw += dn;
                 --r;
                 left = true;
-            } else if (!(bits & 1u)) {
+            } else if (bits == 2u) {
                 p1 += (gnl >> 8) * (gnl & 255);
                 sumw += gnl >> 8;
                 --r;
