@@ -409,12 +409,15 @@ def ours(args, rank, world, local_rank):
     for _ in range(min(W, 1)):
         st2 = step(reads_ts, False)
     barrier()
+    ctx.profile(True)
     ctx.timer_start()
     t0 = time.perf_counter()
     for _ in range(K):
         st2 = step(reads_ts, True)
     barrier()
     e2e_ms = max(ctx.timer_stop(), (time.perf_counter() - t0) * 1e3)
+    e2e_stages = ctx.profile_stages()
+    ctx.profile(False)
     int_peak = ctx.int_peak_gops()
 
     def allmax(x):
@@ -492,7 +495,8 @@ def ours(args, rank, world, local_rank):
             "index_build_s": index_s, "datagen_s": gen_s, "pack_s": pack_s,
             "e2e": {"value": total_reads / (e2e_step_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": st2["h2d_bytes"], "d2h_bytes_per_step": d2h_links,
-                    "ms_per_step": e2e_step_ms},
+                    "ms_per_step": e2e_step_ms,
+                    "stage_ms_per_step": {k: val / K for k, val in e2e_stages.items()}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {

@@ -34,6 +34,9 @@ struct vsk_trset {
     // rotlists flattened for the device (built on demand, dropped when the lists change)
     std::vector<int32_t> rot_off, rot_mem;
     bool rot_flat = false;
+    // first 64-column block of each consensus (what the LCS kernels index by), built with the flat rotlists
+    std::vector<int64_t> cons_blk;  // [2n+1]
+    bool blk_ready = false;
     std::vector<void *> pinned;  // host ranges registered with cudaHostRegister (vsk_trset_pin)
     // Raw mode (vsk_trset_load_leb36_raw): profiles and flanks are still the file's text and are decoded on
     // the device when the set is uploaded (LEB36 digits -> ids, consensus, flank clean-up).  ids / cons / fl
@@ -45,6 +48,9 @@ struct vsk_trset {
     std::vector<int64_t> raw_flank;    // [2n] offset of the left / right flank text of each record
     std::vector<int32_t> raw_flen;     // [2n] their lengths
 };
+
+// builds the derived host arrays an upload needs (flat rotlists, cons_blk) if they are not there yet
+void vsk_trset_prepare(vsk_trset *ts);
 
 // Seed geometry per TRANGE (psearch.c:161-318)
 struct vsk_seedinfo {

@@ -384,6 +384,9 @@ extern "C" int vsk_trset_apply_rotindex(vsk_trset *ts, const char *path) {
     if (!ts || !path) return VSK_ERR_ARG;
     FILE *fp = fopen(path, "r");
     if (!fp) return VSK_OK;  // "no rotated file is fine"
+    // the lists are about to change: page-locked ranges (vsk_trset_pin) are released, pin again afterwards
+    for (void *p : ts->pinned) cudaHostUnregister(p);
+    ts->pinned.clear();
     std::vector<char> line(1 << 20);
     std::string all;
     size_t got;
@@ -434,11 +437,32 @@ extern "C" int vsk_trset_apply_rotindex(vsk_trset *ts, const char *path) {
     return VSK_OK;
 }
 
+void vsk_trset_prepare(vsk_trset *ts) {
+    if (!ts->rot_flat) {  // rotlists flattened once (cache inside the TR set)
+        ts->rot_off.assign((size_t)ts->n + 1, 0);
+        ts->rot_mem.clear();
+        for (int32_t i = 0; i < ts->n; ++i) {
+            ts->rot_off[(size_t)i] = (int32_t)ts->rot_mem.size();
+            ts->rot_mem.insert(ts->rot_mem.end(), ts->rotlist[(size_t)i].begin(), ts->rotlist[(size_t)i].end());
+        }
+        ts->rot_off[(size_t)ts->n] = (int32_t)ts->rot_mem.size();
+        ts->rot_flat = true;
+    }
+    if (!ts->blk_ready && (!ts->raw || ts->raw_decoded)) {
+        const size_t np = (size_t)2 * ts->n;
+        ts->cons_blk.assign(np + 1, 0);
+        for (size_t p = 0; p < np; ++p)
+            ts->cons_blk[p + 1] = ts->cons_blk[p] + (ts->cons_off[p + 1] - ts->cons_off[p] + 63) / 64;
+        ts->blk_ready = true;
+    }
+}
+
 // Page-lock the large arrays of a TR set so that vsk_proclu_run's host->device copies run at
 // full PCIe rate (one-time cost; undone by vsk_trset_free).
 extern "C" int vsk_trset_pin(vsk_trset *ts) {
     if (!ts) return VSK_ERR_ARG;
     if (!ts->pinned.empty()) return VSK_OK;
+    vsk_trset_prepare(ts);
     auto pin = [&](void *p, size_t bytes) {
         if (bytes < (1u << 16)) return;
         if (cudaHostRegister(p, bytes, cudaHostRegisterPortable) == cudaSuccess) ts->pinned.push_back(p);
@@ -454,6 +478,13 @@ extern "C" int vsk_trset_pin(vsk_trset *ts) {
     pin(ts->rightlen.data(), ts->rightlen.size() * sizeof(int32_t));
     pin(ts->patlen.data(), ts->patlen.size() * sizeof(int32_t));
     pin(ts->key.data(), ts->key.size() * sizeof(int32_t));
+    if (ts->rot_flat) {
+        pin(ts->rot_off.data(), ts->rot_off.size() * sizeof(int32_t));
+        pin(ts->rot_mem.data(), ts->rot_mem.size() * sizeof(int32_t));
+    }
+    if (ts->blk_ready) pin(ts->cons_blk.data(), ts->cons_blk.size() * sizeof(int64_t));
+    pin(ts->master.data(), ts->master.size());
+    pin(ts->dir.data(), ts->dir.size());
     return VSK_OK;
 }
 

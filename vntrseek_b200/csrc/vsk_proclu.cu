@@ -350,17 +350,7 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out, bool
     r->host = ts;
     r->d.n = ts->n;
     int rc;
-    if (!ts->rot_flat) {  // flatten the rotlists once (cache inside the TR set)
-        vsk_trset *mt = const_cast<vsk_trset *>(ts);
-        mt->rot_off.assign((size_t)ts->n + 1, 0);
-        mt->rot_mem.clear();
-        for (int32_t i = 0; i < ts->n; ++i) {
-            mt->rot_off[(size_t)i] = (int32_t)mt->rot_mem.size();
-            mt->rot_mem.insert(mt->rot_mem.end(), ts->rotlist[(size_t)i].begin(), ts->rotlist[(size_t)i].end());
-        }
-        mt->rot_off[(size_t)ts->n] = (int32_t)mt->rot_mem.size();
-        mt->rot_flat = true;
-    }
+    if (!ts->rot_flat || (!ts->raw && !ts->blk_ready)) vsk_trset_prepare(const_cast<vsk_trset *>(ts));
 #define UP(field, vec) \
     if ((rc = upload_vec(ctx, r->allocs, vec, &r->d.field, &r->h2d_bytes))) { *out = r; return rc; }
 #define UPB(field, vec)                                                                                   \
@@ -401,10 +391,9 @@ static int upload_trset(vsk_ctx *ctx, const vsk_trset *ts, vsk_reads **out, bool
 #undef UPB
     {
         const size_t np = (size_t)2 * ts->n;
-        std::vector<int64_t> blk(np + 1, 0);
-        for (size_t p = 0; p < np; ++p) blk[p + 1] = blk[p] + (ts->cons_off[p + 1] - ts->cons_off[p] + 63) / 64;
-        const int64_t nblk = blk[np];
-        if ((rc = upload_vec(ctx, r->allocs, blk, &r->d.cons_blk, &r->h2d_bytes))) { *out = r; return rc; }
+        if (!ts->blk_ready) vsk_trset_prepare(const_cast<vsk_trset *>(ts));  // raw set: cons_off is known only now
+        const int64_t nblk = ts->cons_blk[np];
+        if ((rc = upload_vec(ctx, r->allocs, ts->cons_blk, &r->d.cons_blk, &r->h2d_bytes))) { *out = r; return rc; }
         VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)&r->d.cons_planes, sizeof(uint64_t) * 4 * (size_t)(nblk + 1), ctx->pool, ctx->stream));
         r->allocs.push_back(r->d.cons_planes);
         VSK_CUDA(ctx, cudaMallocFromPoolAsync((void **)&r->d.cons_codes, sizeof(uint64_t) * 2 * (size_t)(nblk + 1), ctx->pool, ctx->stream));
@@ -1574,7 +1563,9 @@ extern "C" int vsk_proclu_run(vsk_ctx *ctx, const vsk_refs *R, const vsk_trset *
     if (!ctx || !R || !reads || !out) return VSK_ERR_ARG;
     vsk_reads *Q = nullptr;
     VSK_CUDA(ctx, cudaSetDevice(ctx->device));
+    vsk_stage_mark(ctx, nullptr);
     int rc = upload_trset(ctx, reads, &Q, /*defer_big=*/!reads->raw);
+    vsk_stage_mark(ctx, "upload");
     if (rc) { free_reads(Q); return rc; }
     const int64_t h2d = Q->h2d_bytes;
     rc = vsk_proclu_run_resident(ctx, R, Q, prm, out);
