@@ -79,51 +79,89 @@ def host_info():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region"""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    """nvidia-smi clocks / throttle reasons during the timed region (the profiling recipe's line: ONE process
+    that samples every GPU of the box every 200 ms).  It is started before the warm-up steps -- nvidia-smi takes
+    a second or two to attach to eight GPUs, and eight of them starting inside a one-second timed region slowed
+    the kernels they were meant to observe -- and only the samples stamped inside [mark(), stop()] count."""
+    Q = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, dev, period_ms=200):
+    def __init__(self, period_ms=200, enabled=True):
         self.p = None
-        if period_ms <= 0:
+        self.t_mark = None
+        if period_ms <= 0 or not enabled:
             return
         try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(dev), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", str(int(period_ms))],
+            self.p = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", str(int(period_ms))],
                                       stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.first = self.p.stdout.readline()  # attached: the first sample is out
         except OSError:
-            pass
+            self.p = None
 
-    def stop(self):
+    def mark(self):
+        """start of the timed region"""
+        import datetime
+        self.t_mark = datetime.datetime.now()
+
+    def stop(self, gpus=None):
+        """gpus: nvidia-smi indices to report (None = all).  sm_mhz = the lowest per-GPU median under load."""
+        import datetime
+        t_end = datetime.datetime.now()
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
         if not self.p:
             return out
         self.p.terminate()
         try:
-            txt = self.p.communicate(timeout=5)[0]
+            txt = self.first + self.p.communicate(timeout=5)[0]
         except Exception:
             return out
-        sm, mx, reasons = [], [], set()
+        per, mx, reasons, power = {}, [], set(), {}
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in txt.splitlines():
             f = [x.strip() for x in line.split(",")]
-            if len(f) < 7:
+            if len(f) < 9:
                 continue
             try:
-                sm.append(float(f[0]))
-                mx.append(float(f[1]))
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f")
+                gi = int(f[1])
+                if self.t_mark is not None and not (self.t_mark <= ts <= t_end):
+                    continue
+                if gpus is not None and gi not in gpus:
+                    continue
+                per.setdefault(gi, []).append(float(f[2]))
+                mx.append(float(f[3]))
+                power.setdefault(gi, []).append(float(f[4]))
             except ValueError:
                 continue
-            for n, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
+            for n, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
                     reasons.add(n)
-        if sm:
-            out["sm_mhz"] = float(np.median(sm))
+        if per:
+            med = {g: float(np.median(x)) for g, x in per.items()}
+            out["sm_mhz"] = min(med.values())
             out["sm_max_mhz"] = float(max(mx))
+            out["samples"] = int(sum(len(x) for x in per.values()))
+            if len(med) > 1:
+                out["per_gpu_sm_mhz"] = [med[g] for g in sorted(med)]
+                out["per_gpu_power_w"] = [float(np.median(power[g])) for g in sorted(power)]
+            else:
+                out["power_w"] = float(np.median(next(iter(power.values()))))
         out["reasons"] = sorted(reasons)
-        out["samples"] = len(sm)
         return out
+
+
+def visible_gpus(world):
+    """nvidia-smi indices of the GPUs this job runs on"""
+    cvd = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if cvd:
+        try:
+            ids = [int(x) for x in cvd.split(",") if x.strip() != ""]
+            return set(ids[:world]) if world > 1 else set(ids[:1])
+        except ValueError:
+            return None
+    return set(range(world))
 
 
 # --------------------------------------------------------------------------- reference arm
@@ -379,13 +417,14 @@ def ours(args, rank, world, local_rank):
         return st
 
     # ---- device-resident leg ------------------------------------------------
+    sampler = ClockSampler(args.clock_ms, enabled=(rank == 0))  # attached before the warm-up, see the class
     # untimed pass with exact cell accounting (the same batch is scanned every step)
     _, stats_cells = v.proclu(ctx, idx, resident, count_cells=True)
     stats = None
     for _ in range(W):
         stats = step(resident, False)
     barrier()
-    sampler = ClockSampler(local_rank, args.clock_ms)
+    sampler.mark()
     ctx.profile(True)
     l0 = ctx.launches
     ctx.timer_start()
@@ -400,7 +439,7 @@ def ours(args, rank, world, local_rank):
     sweep_ms, sweep_launches, sweep_busy_ms = ctx.profile_read_sweep()
     stages = ctx.profile_stages()
     ctx.profile(False)
-    clocks = sampler.stop()
+    clocks = sampler.stop(visible_gpus(world))
     ag_resident_ms = ag_ms[0] / K
     ag_ms[0] = 0.0
     ag_phases = {k: val / (K + W) for k, val in gatherer.phase_ms.items()} if gatherer else {}
@@ -447,7 +486,6 @@ def ours(args, rank, world, local_rank):
     rank_scan_ms = allgather_floats(sum(stages.values()) / K)
     rank_cells = allgather_floats(float(stats_cells["dp_cells"]))
     rank_dp_ms = allgather_floats(dp_ms / K)
-    rank_sm_mhz = allgather_floats(float(clocks.get("sm_mhz") or 0.0))
     step_ms = allmax(max(dev_ms, wall_ms)) / K
     e2e_step_ms = allmax(e2e_ms) / K
     total_reads = allsum(float(len(reads)))
@@ -541,7 +579,7 @@ def ours(args, rank, world, local_rank):
                                       "rank waits for the slowest rank's scan to finish (per_rank below)")
             line["per_rank"] = {"ms_per_step": rank_step_ms, "scan_ms_per_step": rank_scan_ms,
                                 "allgather_ms_per_step": rank_ag_ms, "dp_cells_per_step": rank_cells,
-                                "dp_stage_ms_per_step": rank_dp_ms, "sm_mhz": rank_sm_mhz,
+                                "dp_stage_ms_per_step": rank_dp_ms,
                                 "rank0_merge_phases_host_ms": ag_phases}
         if parity is not None:
             line["parity_at_scale"] = parity
@@ -677,13 +715,13 @@ def flank_workload(args, rank, world, local_rank):
     cwd = os.getcwd()
     os.chdir(outdir)
     st = FlankStats()
-    sampler = None
+    sampler = ClockSampler()
     e2e, kern = [], []
     l0 = 0
     try:
         for k in range(W + K):
             if k == W:
-                sampler = ClockSampler(local_rank)
+                sampler.mark()
                 l0 = ctx.launches
             t = time.perf_counter()
             rc = L.vsk_flankalign_run(ctx.h, flanks.encode(), 0, 50, 15, 0, C.byref(st))
@@ -694,7 +732,7 @@ def flank_workload(args, rank, world, local_rank):
                 kern.append(st.kernel_ms)
     finally:
         os.chdir(cwd)
-    clocks = sampler.stop()
+    clocks = sampler.stop(visible_gpus(1))
     launches = ctx.launches - l0
     int_peak = ctx.int_peak_gops()
     ms_k, ms_e = float(np.mean(kern)), float(np.mean(e2e))
@@ -797,7 +835,8 @@ def sweep_workload(args, rank, world, local_rank):
     per = []
     tot_cells = tot_ms = tot_e2e_ms = 0.0
     h2d = d2h = 0
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler()
+    sampler.mark()
     l0 = ctx.launches
     for L, n, o1, i1, i2 in cases:
         pa, pb = ctx.profiles(off=o1, ids=i1), ctx.profiles(off=o1, ids=i2)
@@ -829,7 +868,7 @@ def sweep_workload(args, rank, world, local_rank):
         pb.close()
         per.append(row)
     launches = ctx.launches - l0
-    clocks = sampler.stop()
+    clocks = sampler.stop(visible_gpus(1))
     val = tot_cells / (tot_ms * 1e-3) / 1e9
     cpu = {"err": "skipped"}
     if not args.no_cpu_baseline:

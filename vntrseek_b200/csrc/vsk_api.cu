@@ -129,8 +129,8 @@ extern "C" void vsk_destroy(vsk_ctx *ctx) {
     cudaFree(ctx->d_links);
     for (int i = 0; i < 2; ++i)
         if (ctx->dd_stream[i]) cudaStreamDestroy(ctx->dd_stream[i]);
-    for (int i = 0; i < 4; ++i)
-        if (ctx->dd_ev[i]) cudaEventDestroy(ctx->dd_ev[i]);
+    for (cudaEvent_t e : ctx->dd_ev)
+        if (e) cudaEventDestroy(e);
     for (auto &b : ctx->pin_free) cudaFreeHost(b.first);
     for (void *m : ctx->dd_mem) cudaFree(m);
     if (ctx->h_present_pin) cudaFreeHost(ctx->h_present_pin);

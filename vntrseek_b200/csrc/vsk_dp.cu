@@ -814,7 +814,7 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         grid_w = grid;
         stride_w = stride;
         if (dir_any) {  // the direction-bit path forks here and overlaps the kernels below
-            int rc = vsk_dp_dir_begin(ctx);
+            int rc = vsk_dp_dir_begin(ctx, d_jobs, n_warp, dir_q8 ? n_q8 : 0);
             if (rc) return rc;
         }
         if (n_warp > 0) {
@@ -826,66 +826,91 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
             VSK_CUDA(ctx, cudaGetLastError());
         }
     }
-    if (n_q8 > 0 && !dir_q8) {
-        const size_t smem = 2048 + 1024 + (size_t)K * K;
-        if (!((g_q8_attr_set >> (ctx->device & 63)) & 1)) {
-            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_q8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               2048 + 1024 + 200 * 200));
-            g_q8_attr_set |= 1ull << (ctx->device & 63);
+    auto small_pairs = [&]() -> int {
+        if (n_q8 > 0 && !dir_q8) {
+            const size_t smem = 2048 + 1024 + (size_t)K * K;
+            if (!((g_q8_attr_set >> (ctx->device & 63)) & 1)) {
+                VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_q8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   2048 + 1024 + 200 * 200));
+                g_q8_attr_set |= 1ull << (ctx->device & 63);
+            }
+            int per_sm = 0;
+            VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_q8_kernel, Q8_WARPS * 32, smem));
+            if (per_sm < 1) per_sm = 1;
+            int64_t grid = (int64_t)ctx->sm_count * per_sm;
+            const int64_t need = (n_q8 + Q8_WARPS * 4 - 1) / (Q8_WARPS * 4);
+            if (grid > need) grid = need;
+            VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue + 1, 0, sizeof(int), ctx->stream));
+            vsk_dp_q8_kernel<<<(unsigned)grid, Q8_WARPS * 32, smem, ctx->stream>>>(
+                d_left_ids, d_top_ids, d_jobs + n_warp, (int)n_q8, ctx->d_tiny_dense, ctx->d_tiny_ktab, K, ctx->d_gapnd,
+                ctx->d_queue + 1, d_out);
+            ctx->launches++;
+            VSK_CUDA(ctx, cudaGetLastError());
         }
-        int per_sm = 0;
-        VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_q8_kernel, Q8_WARPS * 32, smem));
-        if (per_sm < 1) per_sm = 1;
-        int64_t grid = (int64_t)ctx->sm_count * per_sm;
-        const int64_t need = (n_q8 + Q8_WARPS * 4 - 1) / (Q8_WARPS * 4);
-        if (grid > need) grid = need;
-        VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue + 1, 0, sizeof(int), ctx->stream));
-        vsk_dp_q8_kernel<<<(unsigned)grid, Q8_WARPS * 32, smem, ctx->stream>>>(
-            d_left_ids, d_top_ids, d_jobs + n_warp, (int)n_q8, ctx->d_tiny_dense, ctx->d_tiny_ktab, K, ctx->d_gapnd,
-            ctx->d_queue + 1, d_out);
-        ctx->launches++;
-        VSK_CUDA(ctx, cudaGetLastError());
-    }
-    if (n_tiny > 0 && use_tinydir) {
-        const size_t smem = (size_t)(2 * TINY_MAXCOLS + 1) * TD_THREADS * 2 + 2048 + 1024 + (size_t)K * K;
-        static uint64_t attr_td = 0;
-        if (!((attr_td >> (ctx->device & 63)) & 1)) {
-            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_tinydir_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               (int)((2 * TINY_MAXCOLS + 1) * TD_THREADS * 2 + 2048 + 1024 + 200 * 200)));
-            attr_td |= 1ull << (ctx->device & 63);
-        }
-        const unsigned gridt = (unsigned)((n_tiny + TD_THREADS - 1) / TD_THREADS);
-        if (K > 0)
-            vsk_dp_tinydir_kernel<true><<<gridt, TD_THREADS, smem, ctx->stream>>>(
+        if (n_tiny > 0 && use_tinydir) {
+            const size_t smem = (size_t)(2 * TINY_MAXCOLS + 1) * TD_THREADS * 2 + 2048 + 1024 + (size_t)K * K;
+            static uint64_t attr_td = 0;
+            if (!((attr_td >> (ctx->device & 63)) & 1)) {
+                VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_tinydir_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   (int)((2 * TINY_MAXCOLS + 1) * TD_THREADS * 2 + 2048 + 1024 + 200 * 200)));
+                attr_td |= 1ull << (ctx->device & 63);
+            }
+            const unsigned gridt = (unsigned)((n_tiny + TD_THREADS - 1) / TD_THREADS);
+            if (K > 0)
+                vsk_dp_tinydir_kernel<true><<<gridt, TD_THREADS, smem, ctx->stream>>>(
+                    d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,
+                    ctx->d_dist, ctx->d_gapnd, d_out);
+            else
+                vsk_dp_tinydir_kernel<false><<<gridt, TD_THREADS, smem, ctx->stream>>>(
+                    d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, nullptr, nullptr, 0, ctx->d_dist,
+                    ctx->d_gapnd, d_out);
+            ctx->launches++;
+            VSK_CUDA(ctx, cudaGetLastError());
+        } else if (n_tiny > 0) {
+            const size_t smem = (size_t)(2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 + 2048 + 1024 +
+                                (size_t)K * K;
+            if (!((g_tiny_attr_set >> (ctx->device & 63)) & 1)) {
+                VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   (int)((2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 +
+                                                         2048 + 1024 + 200 * 200)));
+                g_tiny_attr_set |= 1ull << (ctx->device & 63);
+            }
+            vsk_dp_tiny_kernel<<<(unsigned)((n_tiny + TINY_THREADS - 1) / TINY_THREADS), TINY_THREADS, smem, ctx->stream>>>(
                 d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,
-                ctx->d_dist, ctx->d_gapnd, d_out);
-        else
-            vsk_dp_tinydir_kernel<false><<<gridt, TD_THREADS, smem, ctx->stream>>>(
-                d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, nullptr, nullptr, 0, ctx->d_dist,
                 ctx->d_gapnd, d_out);
-        ctx->launches++;
-        VSK_CUDA(ctx, cudaGetLastError());
-    } else if (n_tiny > 0) {
-        const size_t smem = (size_t)(2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 + 2048 + 1024 +
-                            (size_t)K * K;
-        if (!((g_tiny_attr_set >> (ctx->device & 63)) & 1)) {
-            VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                               (int)((2 * (TINY_MAXCOLS + 1) + TINY_MAXCOLS) * TINY_THREADS * 4 +
-                                                     2048 + 1024 + 200 * 200)));
-            g_tiny_attr_set |= 1ull << (ctx->device & 63);
+            ctx->launches++;
+            VSK_CUDA(ctx, cudaGetLastError());
         }
-        vsk_dp_tiny_kernel<<<(unsigned)((n_tiny + TINY_THREADS - 1) / TINY_THREADS), TINY_THREADS, smem, ctx->stream>>>(
-            d_left_ids, d_top_ids, d_jobs + n_warp + n_q8, (int)n_tiny, ctx->d_tiny_dense, ctx->d_tiny_ktab, K,
-            ctx->d_gapnd, d_out);
-        ctx->launches++;
-        VSK_CUDA(ctx, cudaGetLastError());
-    }
-    if (dir_any) {
+        return VSK_OK;
+    };
+    // Where the small-pair kernels go relative to the sweeps of the direction-bit path (VSK_DP_SMALL_ORDER):
+    // 0 = enqueued first on ctx->stream, running beside the first sweeps; 1 = the sweeps wait for them;
+    // 2 = after the last sweep, beside the 8-lane kernels and traces that end the stage; 3 = after the join
+    // (default).  Measured on the 1 M-read bench, DP stage: 224 / 227 / 222 / 217 ms -- the thread-per-pair
+    // kernel and the sweep slow each other down when they share SMs, so they run one after the other.
+    static const int small_order = [] {
+        const char *e = getenv("VSK_DP_SMALL_ORDER");
+        const int v = e ? atoi(e) : 3;
+        return (v >= 0 && v <= 3) ? v : 3;
+    }();
+    if (!dir_any) {
+        if (int rc = small_pairs()) return rc;
+    } else {
+        if (small_order <= 1) {
+            if (int rc = small_pairs()) return rc;
+            if (small_order == 1) VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[0], ctx->stream));  // fork point moves behind them
+        }
         vsk_dp_job *d_redo = nullptr;
         int *d_redo_n = nullptr;
         int rc = vsk_dp_dir_launch(ctx, d_left_ids, d_top_ids, d_jobs, n_warp, dir_q8 ? n_q8 : 0, K, max_l1, d_out,
                                    &d_redo, &d_redo_n);
         if (rc) return rc;
+        if (small_order == 2) {
+            if ((rc = vsk_dp_dir_wait_sweeps(ctx))) return rc;
+            if ((rc = small_pairs())) return rc;
+        }
+        if ((rc = vsk_dp_dir_join(ctx))) return rc;
+        if (small_order == 3 && (rc = small_pairs())) return rc;
         if (d_redo) {  // pairs whose corner the band does not reach
             VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
             vsk_dp_kernel<<<(unsigned)grid_w, DP_WARPS * 32, DP_SMEM_BYTES, ctx->stream>>>(

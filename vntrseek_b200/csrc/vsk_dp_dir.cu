@@ -711,15 +711,6 @@ __global__ void vsk_dd_bounds_kernel(const int64_t *__restrict__ off, int n, int
 
 static uint64_t g_dd_attr_set = 0;  // one bit per device ordinal
 
-int vsk_dp_dir_begin(vsk_ctx *ctx) {
-    for (int i = 0; i < 2; ++i)
-        if (!ctx->dd_stream[i]) VSK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->dd_stream[i], cudaStreamNonBlocking));
-    for (int i = 0; i < 4; ++i)
-        if (!ctx->dd_ev[i]) VSK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->dd_ev[i], cudaEventDisableTiming));
-    VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[0], ctx->stream));
-    return VSK_OK;
-}
-
 // grow-only buffer k of the context
 static int dd_reserve(vsk_ctx *ctx, int k, size_t bytes, void **out) {
     if (bytes > ctx->dd_cap[k]) {
@@ -731,6 +722,50 @@ static int dd_reserve(vsk_ctx *ctx, int k, size_t bytes, void **out) {
         ctx->dd_cap[k] = want;
     }
     *out = ctx->dd_mem[k];
+    return VSK_OK;
+}
+
+static int dd_force() {  // tuning aid: VSK_DD_FORCE=8|12|16 fixes the columns per lane of the sweep
+    static const int force = [] {
+        const char *e = getenv("VSK_DD_FORCE");
+        const int c = e ? atoi(e) : 0;
+        return (c == 8 || c == 12 || c == 16) ? c : 0;
+    }();
+    return force;
+}
+
+// Sizes the direction words of the jobs (the one host round trip of the path) and marks the fork point.  It runs
+// BEFORE the other DP kernels are enqueued: the device is idle for the few microseconds of the two small
+// kernels, and from then on everything of the DP stage is queued without a host synchronisation, so a host
+// thread that is late (other processes on the cores) cannot leave the device without work in mid-stage.
+int vsk_dp_dir_begin(vsk_ctx *ctx, const vsk_dp_job *d_jobs, int64_t n_warp, int64_t n_q8) {
+    for (int i = 0; i < 2; ++i)
+        if (!ctx->dd_stream[i]) VSK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->dd_stream[i], cudaStreamNonBlocking));
+    for (int i = 0; i < 7; ++i)
+        if (!ctx->dd_ev[i]) VSK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->dd_ev[i], cudaEventDisableTiming));
+    const int64_t n = n_warp + n_q8;
+    ctx->dd_plan_n = n;
+    ctx->dd_plan_total = ctx->dd_plan_off_q8 = 0;
+    if (n > 0) {
+        int rc;
+        int64_t *d_words = nullptr, *d_off = nullptr;
+        void *d_tmp = nullptr;
+        size_t tmp_bytes = 0;
+        cudaStream_t st = ctx->stream;
+        VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_words, d_off, (int)(n + 1), st));
+        if ((rc = dd_reserve(ctx, 0, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_words))) return rc;
+        if ((rc = dd_reserve(ctx, 1, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_off))) return rc;
+        if ((rc = dd_reserve(ctx, 2, tmp_bytes + 16, &d_tmp))) return rc;
+        VSK_CUDA(ctx, cudaMemsetAsync(d_words + n, 0, sizeof(int64_t), st));
+        vsk_dd_words_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(d_jobs, (int)n, (int)n_warp, dd_force(), d_words);
+        ctx->launches++;
+        VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_words, d_off, (int)(n + 1), st));
+        ctx->launches += 2;
+        VSK_CUDA(ctx, cudaMemcpyAsync(&ctx->dd_plan_total, d_off + n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        VSK_CUDA(ctx, cudaMemcpyAsync(&ctx->dd_plan_off_q8, d_off + n_warp, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        VSK_CUDA(ctx, cudaStreamSynchronize(st));
+    }
+    VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[0], ctx->stream));
     return VSK_OK;
 }
 
@@ -748,28 +783,14 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     if (n <= 0) return VSK_OK;
     cudaStream_t s0 = ctx->dd_stream[0], s1 = ctx->dd_stream[1];
     int rc;
-    int64_t *d_words = nullptr, *d_off = nullptr;
-    void *d_tmp = nullptr;
-    size_t tmp_bytes = 0;
-    VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
-    if ((rc = dd_reserve(ctx, 0, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_words))) return rc;
-    if ((rc = dd_reserve(ctx, 1, (size_t)(n + 1) * sizeof(int64_t), (void **)&d_off))) return rc;
-    if ((rc = dd_reserve(ctx, 2, tmp_bytes + 16, &d_tmp))) return rc;
+    if (ctx->dd_plan_n != n) return vsk_fail(ctx, VSK_ERR_ARG, "vsk_dp_dir_launch without its vsk_dp_dir_begin");
+    ctx->dd_plan_n = -1;
+    const int force = dd_force();
+    int64_t *d_off = (int64_t *)ctx->dd_mem[1];           // prefix sums of the jobs' direction words (vsk_dp_dir_begin)
+    const int64_t total = ctx->dd_plan_total, off_q8 = ctx->dd_plan_off_q8;  // all words; words before the first 8-lane job
     VSK_CUDA(ctx, cudaStreamWaitEvent(s0, ctx->dd_ev[0], 0));
-    VSK_CUDA(ctx, cudaMemsetAsync(d_words + n, 0, sizeof(int64_t), s0));
-    static const int force = [] {  // tuning aid: VSK_DD_FORCE=8|12|16 fixes the columns per lane of the sweep
-        const char *e = getenv("VSK_DD_FORCE");
-        const int c = e ? atoi(e) : 0;
-        return (c == 8 || c == 12 || c == 16) ? c : 0;
-    }();
-    vsk_dd_words_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s0>>>(d_jobs, (int)n, (int)n_warp, force, d_words);
-    ctx->launches++;
-    VSK_CUDA(ctx, cub::DeviceScan::ExclusiveSum(d_tmp, tmp_bytes, d_words, d_off, (int)(n + 1), s0));
-    ctx->launches += 2;
-    int64_t total = 0, off_q8 = 0;  // all words; words before the first 8-lane job
-    VSK_CUDA(ctx, cudaMemcpyAsync(&total, d_off + n, sizeof(int64_t), cudaMemcpyDeviceToHost, s0));
-    VSK_CUDA(ctx, cudaMemcpyAsync(&off_q8, d_off + n_warp, sizeof(int64_t), cudaMemcpyDeviceToHost, s0));
-    VSK_CUDA(ctx, cudaStreamSynchronize(s0));
+    ctx->dd_sweeps_marked = 0;
+    ctx->dd_join_pending = false;
     if (total == 0) {
         VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[2], s0));
         VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[2], 0));
@@ -855,6 +876,8 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
                 ctx->prof_sweep_events.push_back(pe0);
                 ctx->prof_sweep_events.push_back(pe1);
             }
+            VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[4 + (b & 1)], st));  // the stream's last sweep so far
+            ctx->dd_sweeps_marked |= 1 << (b & 1);
         }
         if (n_q8 > 0 && b >= h_q8_first) {
             if (dense)
@@ -873,9 +896,23 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
         ctx->launches++;
     }
     VSK_CUDA(ctx, cudaGetLastError());
-    // join: ctx->stream continues after both side streams
     VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[2], s0));
     VSK_CUDA(ctx, cudaEventRecord(ctx->dd_ev[3], s1));
+    ctx->dd_join_pending = true;
+    return VSK_OK;
+}
+
+// ctx->stream waits for the sweeps (not for the 8-lane kernels and the traces behind them)
+int vsk_dp_dir_wait_sweeps(vsk_ctx *ctx) {
+    for (int i = 0; i < 2; ++i)
+        if (ctx->dd_sweeps_marked & (1 << i)) VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[4 + i], 0));
+    return VSK_OK;
+}
+
+// join: ctx->stream continues after both side streams
+int vsk_dp_dir_join(vsk_ctx *ctx) {
+    if (!ctx->dd_join_pending) return VSK_OK;
+    ctx->dd_join_pending = false;
     VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[2], 0));
     VSK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->dd_ev[3], 0));
     return VSK_OK;

@@ -44,7 +44,10 @@ struct vsk_ctx {
     // side streams of the direction-bit DP path: batches alternate between them so that the tail of
     // one forward sweep is filled by the next (created on first use)
     cudaStream_t dd_stream[2] = {nullptr, nullptr};
-    cudaEvent_t dd_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t dd_ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int dd_sweeps_marked = 0;
+    bool dd_join_pending = false;
+    int64_t dd_plan_total = 0, dd_plan_off_q8 = 0, dd_plan_n = -1;  // vsk_dp_dir_begin -> vsk_dp_dir_launch
     // ... and its work buffers (direction words, boundary scratch, offsets, redo list): grow-only,
     // kept for the life of the context so that no launch waits for an allocation
     void *dd_mem[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -134,9 +137,11 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
 // vsk_dp_dir_begin marks the point of ctx->stream the side streams start from (call it before the
 // other DP kernels are enqueued so that they overlap); vsk_dp_dir_launch joins back into ctx->stream.
 // *redo / *redo_count point into the context's buffers (valid until the next call).
-int vsk_dp_dir_begin(vsk_ctx *ctx);
+int vsk_dp_dir_begin(vsk_ctx *ctx, const vsk_dp_job *d_jobs, int64_t n_warp, int64_t n_q8);
 // d_jobs[0..n_warp) are the warp-per-pair jobs, d_jobs[n_warp..n_warp+n_q8) the 8-lane jobs (dense
 // K x K table of the context).
+int vsk_dp_dir_wait_sweeps(vsk_ctx *ctx);
+int vsk_dp_dir_join(vsk_ctx *ctx);
 int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_top_ids, const vsk_dp_job *d_jobs,
                       int64_t n_warp, int64_t n_q8, int K, int32_t max_l1, int4 *d_out, vsk_dp_job **redo,
                       int **redo_count);
