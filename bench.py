@@ -42,7 +42,7 @@ import numpy as np  # noqa: E402
 
 # bytes: dram read+write of one vsk_dp_dir_kernel launch at the default workload (ncu --set full,
 # profiles/): refreshed whenever the kernel or the batch size changes
-DIR_TRAFFIC = {"bytes": 11.73e9, "source": "profiles/r02_summary.md section C (launch 0: a 12 GiB batch of the first chunk)"}
+DIR_TRAFFIC = {"bytes": 11.73e9, "source": "profiles/r02_summary.md section D (launch 0: a 12 GiB batch of the first chunk)"}
 METRIC = "proclu_read_TRs_mapped_per_sec"
 UNIT = "read-TRs/s"
 OPS_PER_CELL = 14        # algorithmic integer operations per profile-DP cell
@@ -82,16 +82,38 @@ class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (the profiling recipe's line: ONE process
     that samples every GPU of the box every 200 ms).  It is started before the warm-up steps -- nvidia-smi takes
     a second or two to attach to eight GPUs, and eight of them starting inside a one-second timed region slowed
-    the kernels they were meant to observe -- and only the samples stamped inside [mark(), stop()] count."""
-    Q = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    the kernels they were meant to observe -- and only the samples stamped inside [mark(), stop()] count.
+    Per sample and GPU it asks for two values only (SM clock, the bit mask of active clock-event reasons): on an
+    eight-GPU box the recipe's nine fields five times a second cost the ranks 5 % of their step; the constant
+    clocks.max.sm is read once before, the power draw once after."""
+    Q = "timestamp,index,clocks.sm,clocks_event_reasons.active"
+    BITS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+            0x80: "hw_power_brake_slowdown"}
+
+    @staticmethod
+    def _once(fields):
+        try:
+            txt = subprocess.run(["nvidia-smi", "--query-gpu=index," + fields, "--format=csv,noheader,nounits"],
+                                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=30).stdout
+        except (OSError, subprocess.SubprocessError):
+            return {}
+        out = {}
+        for line in txt.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            try:
+                out[int(f[0])] = float(f[1])
+            except (ValueError, IndexError):
+                pass
+        return out
 
     def __init__(self, period_ms=200, enabled=True):
         self.p = None
         self.t_mark = None
+        self.first = ""
+        self.max_mhz = {}
         if period_ms <= 0 or not enabled:
             return
+        self.max_mhz = self._once("clocks.max.sm")
         try:
             self.p = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                        "-lms", str(int(period_ms))],
@@ -117,11 +139,10 @@ class ClockSampler:
             txt = self.first + self.p.communicate(timeout=5)[0]
         except Exception:
             return out
-        per, mx, reasons, power = {}, [], set(), {}
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        per, reasons = {}, set()
         for line in txt.splitlines():
             f = [x.strip() for x in line.split(",")]
-            if len(f) < 9:
+            if len(f) < 4:
                 continue
             try:
                 ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f")
@@ -131,23 +152,20 @@ class ClockSampler:
                 if gpus is not None and gi not in gpus:
                     continue
                 per.setdefault(gi, []).append(float(f[2]))
-                mx.append(float(f[3]))
-                power.setdefault(gi, []).append(float(f[4]))
+                mask = int(f[3], 16)
             except ValueError:
                 continue
-            for n, val in zip(names, f[5:9]):
-                if val.lower().startswith("active"):
-                    reasons.add(n)
+            for bit, name in self.BITS.items():
+                if mask & bit:
+                    reasons.add(name)
         if per:
             med = {g: float(np.median(x)) for g, x in per.items()}
             out["sm_mhz"] = min(med.values())
-            out["sm_max_mhz"] = float(max(mx))
+            mx = [v for g, v in self.max_mhz.items() if g in med]
+            out["sm_max_mhz"] = float(max(mx)) if mx else None
             out["samples"] = int(sum(len(x) for x in per.values()))
             if len(med) > 1:
                 out["per_gpu_sm_mhz"] = [med[g] for g in sorted(med)]
-                out["per_gpu_power_w"] = [float(np.median(power[g])) for g in sorted(power)]
-            else:
-                out["power_w"] = float(np.median(next(iter(power.values()))))
         out["reasons"] = sorted(reasons)
         return out
 

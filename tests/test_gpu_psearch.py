@@ -117,10 +117,12 @@ def test_psearch_golden_small(tmp_path, dst_file):
     assert canonical_clu(os.path.join(w, "reads.leb36.clu")) == canonical_clu(os.path.join(w, "expected.clu"))
 
 
-@pytest.mark.parametrize("switch", ["VSK_DEDUP_BITMAP", "VSK_DP_DIR", "VSK_DP_DIRQ8", "VSK_DP_TINYDIR"])
+@pytest.mark.parametrize("switch", ["VSK_DEDUP_BITMAP", "VSK_DP_DIR", "VSK_DP_DIRQ8", "VSK_DP_TINYDIR",
+                                    "VSK_DP_SMALL_ORDER"])
 def test_alternative_paths_give_the_same_files(tmp_path, dst_file, switch):
     """the run-time switches select the older code paths (radix sort + unique instead of the
-    per-profile bitmap; one-kernel DP instead of sweep + trace): same counters, same .clu"""
+    per-profile bitmap; one-kernel DP instead of sweep + trace; small-pair kernels beside the first
+    sweeps instead of after the join): same counters, same .clu"""
     from conftest import GOLDEN
     g = os.path.join(GOLDEN, "psearch_small")
     outs = []
