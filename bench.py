@@ -501,7 +501,7 @@ def ours(args, rank, world, local_rank):
 
     rank_step_ms = allgather_floats(max(dev_ms, wall_ms) / K)
     rank_ag_ms = allgather_floats(ag_resident_ms)
-    rank_scan_ms = allgather_floats(sum(stages.values()) / K)
+    rank_scan_ms = allgather_floats(sum(val for k, val in stages.items() if not k.startswith("host_")) / K)
     rank_cells = allgather_floats(float(stats_cells["dp_cells"]))
     rank_dp_ms = allgather_floats(dp_ms / K)
     step_ms = allmax(max(dev_ms, wall_ms)) / K

@@ -472,6 +472,11 @@ extern "C" int vsk_profile_stages(vsk_ctx *ctx, char *buf, size_t n) {
         snprintf(tmp, sizeof tmp, "%s=%.3f;", a.first.c_str(), a.second);
         out += tmp;
     }
+    for (auto &a : ctx->host_acc) {  // host wall time inside named sections (not part of the device timeline)
+        snprintf(tmp, sizeof tmp, "host_%s=%.3f;", a.first, a.second);
+        out += tmp;
+    }
+    ctx->host_acc.clear();
     snprintf(buf, n, "%s", out.c_str());
     return VSK_OK;
 }

@@ -758,10 +758,13 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
     if (n_jobs <= 0) return VSK_OK;
     if (n_jobs > 0x7fffffff) return vsk_fail(ctx, VSK_ERR_ARG, "too many DP pairs in one launch");
     int K = 0;
+    const double h0 = vsk_now_ms();
     if (n_tiny > 0 || n_q8 > 0) {
         int rc = tiny_tables(ctx, ids, &K);
         if (rc) return rc;
     }
+    const double h1 = vsk_now_ms();
+    vsk_host_acc(ctx, "dp_tables", h1 - h0);
     static const bool use_dir = [] {
         const char *e = getenv("VSK_DP_DIR");
         return !(e && e[0] == '0');
@@ -795,10 +798,12 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
                                                (int)DP_SMEM_BYTES));
             g_dp_attr_set |= 1ull << (ctx->device & 63);
         }
-        int per_sm = 0;
-        VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_kernel, DP_WARPS * 32,
-                                                                     DP_SMEM_BYTES));
-        if (per_sm < 1) per_sm = 1;
+        if (!ctx->occ_dp) {
+            VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_dp, vsk_dp_kernel, DP_WARPS * 32,
+                                                                         DP_SMEM_BYTES));
+            if (ctx->occ_dp < 1) ctx->occ_dp = 1;
+        }
+        const int per_sm = ctx->occ_dp;
         int64_t grid = (int64_t)ctx->sm_count * per_sm;  // persistent: one wave, work pulled from a queue
         const int64_t need = dir_any ? grid : (n_warp + DP_WARPS - 1) / DP_WARPS;
         if (grid > need) grid = need;
@@ -814,8 +819,10 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         grid_w = grid;
         stride_w = stride;
         if (dir_any) {  // the direction-bit path forks here and overlaps the kernels below
+            const double hb = vsk_now_ms();
             int rc = vsk_dp_dir_begin(ctx, d_jobs, n_warp, dir_q8 ? n_q8 : 0);
             if (rc) return rc;
+            vsk_host_acc(ctx, "dp_plan", vsk_now_ms() - hb);
         }
         if (n_warp > 0) {
             VSK_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(int), ctx->stream));
@@ -925,6 +932,7 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
         ctx->prof_events.push_back(e0);
         ctx->prof_events.push_back(e1);
     }
+    vsk_host_acc(ctx, "dp_launch_total", vsk_now_ms() - h0);
     return VSK_OK;
 }
 

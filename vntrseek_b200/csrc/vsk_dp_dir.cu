@@ -798,16 +798,27 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     }
     // batch size: VSK_DIR_BATCH_MB of direction words per stream (default 12 GiB), at most a sixth of the
     // memory that is free or already ours
-    int64_t batch_mb = 12288;
-    if (const char *e = getenv("VSK_DIR_BATCH_MB")) batch_mb = std::max<int64_t>(16, atoll(e));
-    size_t free_b = 0, total_b = 0;
-    VSK_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
+    const double hs0 = vsk_now_ms();
     const int64_t max_job_words = (int64_t)((VSK_MAXPROF + 255) / 256) * ((max_l1 + 7) & ~7) * 32;  // strips are >= 256 columns
-    int64_t batch_words = std::min<int64_t>(batch_mb << 18, (int64_t)((free_b + ctx->dd_cap[3]) / 6 / 4));
-    batch_words = std::max<int64_t>(batch_words & ~(int64_t)7, max_job_words);
-    const int nb = (int)((total + batch_words - 1) / batch_words);
-    const int64_t half_words = (nb == 1) ? total : batch_words + max_job_words;
-    const int nhalf = nb == 1 ? 1 : 2;
+    // The free-memory query goes through the driver's global lock (slow when something else polls the driver), so
+    // its answer is kept; it is asked again only when the buffer would have to grow.
+    int64_t batch_words = 0, half_words = 0;
+    int nb = 0, nhalf = 0;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        if (!ctx->dd_batch_words || attempt == 1) {
+            int64_t batch_mb = 12288;
+            if (const char *e = getenv("VSK_DIR_BATCH_MB")) batch_mb = std::max<int64_t>(16, atoll(e));
+            size_t free_b = 0, total_b = 0;
+            VSK_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
+            ctx->dd_batch_words = std::min<int64_t>(batch_mb << 18, (int64_t)((free_b + ctx->dd_cap[3]) / 6 / 4)) & ~(int64_t)7;
+            attempt = 1;
+        }
+        batch_words = std::max<int64_t>(ctx->dd_batch_words, max_job_words);
+        nb = (int)((total + batch_words - 1) / batch_words);
+        half_words = (nb == 1) ? total : batch_words + max_job_words;
+        nhalf = nb == 1 ? 1 : 2;
+        if ((size_t)half_words * nhalf * 4 <= ctx->dd_cap[3]) break;  // fits the buffer we have
+    }
 
     if (!((g_dd_attr_set >> (ctx->device & 63)) & 1)) {
         VSK_CUDA(ctx, cudaFuncSetAttribute(vsk_dp_dir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -815,11 +826,12 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
         g_dd_attr_set |= 1ull << (ctx->device & 63);
     }
     const size_t dd_smem = DD_SMEM_BYTES;
-    int per_sm = 0;
-    VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vsk_dp_dir_kernel, DD_WARPS * 32,
-                                                                 dd_smem));
-    if (per_sm < 1) per_sm = 1;
-    const int grid = ctx->sm_count * per_sm;
+    if (!ctx->occ_dd) {
+        VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->occ_dd, vsk_dp_dir_kernel, DD_WARPS * 32,
+                                                                     dd_smem));
+        if (ctx->occ_dd < 1) ctx->occ_dd = 1;
+    }
+    const int grid = ctx->sm_count * ctx->occ_dd;
     // the 8-lane kernel
     const bool dense = K > 0;  // K == 0: no dense table for this data set, the 8-lane kernel reads the global table
     const size_t dq_smem = 2048 + DQ_WARPS * 32 * 64 + 1024 + (size_t)K * K;
@@ -831,12 +843,17 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
                                                2048 + DQ_WARPS * 32 * 64 + 1024 + 200 * 200));
             attr8 |= 1ull << (ctx->device & 63);
         }
-        int per_sm8 = 0;
-        if (dense)
-            VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm8, vsk_dp_q8dir_kernel<true>, DQ_WARPS * 32, dq_smem));
-        else
-            VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm8, vsk_dp_q8dir_kernel<false>, DQ_WARPS * 32, dq_smem));
-        grid8 = ctx->sm_count * (per_sm8 < 1 ? 1 : per_sm8);
+        // occupancy at the largest table (200 x 200): a smaller K could only raise it, the grid is persistent anyway
+        int &per_sm8 = ctx->occ_dq[dense ? 1 : 0];
+        if (!per_sm8) {
+            const size_t worst = 2048 + DQ_WARPS * 32 * 64 + 1024 + (dense ? 200 * 200 : 0);
+            if (dense)
+                VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm8, vsk_dp_q8dir_kernel<true>, DQ_WARPS * 32, worst));
+            else
+                VSK_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm8, vsk_dp_q8dir_kernel<false>, DQ_WARPS * 32, worst));
+            if (per_sm8 < 1) per_sm8 = 1;
+        }
+        grid8 = ctx->sm_count * per_sm8;
     }
     const int stride = ((max_l1 + 31) / 32) * 32 + 128;  // slack: the steady phase fetches up to 96 rows past the last
     const size_t scr_ints = (size_t)grid * DD_WARPS * 2 * stride;
@@ -856,6 +873,7 @@ int vsk_dp_dir_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *
     VSK_CUDA(ctx, cudaStreamWaitEvent(s1, ctx->dd_ev[1], 0));  // s1 starts after the batch bounds exist
 
     const int h_q8_first = (int)(off_q8 / batch_words);  // first batch with 8-lane jobs
+    vsk_host_acc(ctx, "dp_setup", vsk_now_ms() - hs0);
     for (int b = 0; b < nb; ++b) {
         cudaStream_t st = (b & 1) ? s1 : s0;
         uint32_t *dir = d_dir + (size_t)(b & 1) * half_words;

@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <string>
+#include <time.h>
 #include <vector>
 
 #include "../../include/vsk.h"
@@ -75,7 +76,24 @@ struct vsk_ctx {
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     // stage marks of the PROCLU pipeline (profile mode): name of the stage that ENDS at the event
     std::vector<std::pair<const char *, cudaEvent_t>> stage_marks;
+    // host wall time spent in named sections (profile mode), reported by vsk_profile_stages as host_<name>
+    std::vector<std::pair<const char *, double>> host_acc;
+    // answers of driver queries that do not change while the context lives
+    int occ_dp = 0, occ_dd = 0, occ_dq[2] = {0, 0};
+    int64_t dd_batch_words = 0;  // batch size of the direction-word buffer (chosen at the first sizing)
 };
+
+inline double vsk_now_ms() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
+inline void vsk_host_acc(vsk_ctx *ctx, const char *name, double ms) {
+    if (!ctx->profile) return;
+    for (auto &a : ctx->host_acc)
+        if (a.first == name) { a.second += ms; return; }
+    ctx->host_acc.emplace_back(name, ms);
+}
 
 // profile mode: drop an event that closes stage `name` (nullptr = start of a run)
 void vsk_stage_mark(vsk_ctx *ctx, const char *name);
