@@ -253,6 +253,8 @@ static int64_t band_cells(int l1, int l2, int br, double sv) {
     return n;
 }
 
+extern "C" void vsk_dp_batch_free(vsk_ctx *ctx, vsk_dp_batch *b);
+
 extern "C" int vsk_dp_batch_prepare(vsk_ctx *ctx, const vsk_profset *L, const vsk_profset *T, int64_t n,
                                     const int32_t *li, const int32_t *ti, const uint8_t *mode,
                                     int homology, vsk_dp_batch **out) {
@@ -301,13 +303,20 @@ extern "C" int vsk_dp_batch_prepare(vsk_ctx *ctx, const vsk_profset *L, const vs
     b->max_l1 = max_l1;
     b->left = L;
     b->top = T;
-    VSK_CUDA(ctx, cudaSetDevice(ctx->device));
-    VSK_CUDA(ctx, cudaMalloc(&b->d_jobs, sizeof(vsk_dp_job) * (size_t)std::max<int64_t>(n, 1)));
-    VSK_CUDA(ctx, cudaMalloc(&b->d_out, sizeof(int4) * (size_t)std::max<int64_t>(n, 1)));
-    if (n)
-        VSK_CUDA(ctx, cudaMemcpyAsync(b->d_jobs, sorted.data(), sizeof(vsk_dp_job) * (size_t)n,
-                                      cudaMemcpyHostToDevice, ctx->stream));
-    VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int rc = [&]() -> int {  // the batch is released below if any of these fails
+        VSK_CUDA(ctx, cudaSetDevice(ctx->device));
+        VSK_CUDA(ctx, cudaMalloc(&b->d_jobs, sizeof(vsk_dp_job) * (size_t)std::max<int64_t>(n, 1)));
+        VSK_CUDA(ctx, cudaMalloc(&b->d_out, sizeof(int4) * (size_t)std::max<int64_t>(n, 1)));
+        if (n)
+            VSK_CUDA(ctx, cudaMemcpyAsync(b->d_jobs, sorted.data(), sizeof(vsk_dp_job) * (size_t)n,
+                                          cudaMemcpyHostToDevice, ctx->stream));
+        VSK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        return VSK_OK;
+    }();
+    if (rc != VSK_OK) {
+        vsk_dp_batch_free(ctx, b);
+        return rc;
+    }
     *out = b;
     return VSK_OK;
 }
@@ -348,9 +357,18 @@ extern "C" int vsk_pair_dp(vsk_ctx *ctx, const vsk_profset *L, const vsk_profset
 }
 
 // ---- string kernels -----------------------------------------------------------
+// device buffers of one call: freed when the call returns, on every path
+struct DevBufs {
+    std::vector<void *> v;
+    ~DevBufs() {
+        for (void *p : v) cudaFree(p);
+    }
+};
+
 template <typename T>
-static int dev_copy(vsk_ctx *ctx, T **d, const T *h, size_t n) {
+static int dev_copy(vsk_ctx *ctx, DevBufs &bufs, T **d, const T *h, size_t n) {
     VSK_CUDA(ctx, cudaMalloc((void **)d, sizeof(T) * std::max<size_t>(n, 1)));
+    bufs.v.push_back(*d);
     if (n) VSK_CUDA(ctx, cudaMemcpyAsync(*d, h, sizeof(T) * n, cudaMemcpyHostToDevice, ctx->stream));
     return VSK_OK;
 }
@@ -371,20 +389,21 @@ extern "C" int vsk_lcs_pairs(vsk_ctx *ctx, const char *a, const int64_t *a_off, 
     int64_t *doa = nullptr, *dob = nullptr;
     int32_t *dia = nullptr, *dib = nullptr, *dout = nullptr;
     int rc;
-    if ((rc = dev_copy(ctx, &da, (const uint8_t *)a, (size_t)a_off[ma + 1]))) return rc;
-    if ((rc = dev_copy(ctx, &db, (const uint8_t *)b, (size_t)b_off[mb + 1]))) return rc;
-    if ((rc = dev_copy(ctx, &doa, a_off, (size_t)ma + 2))) return rc;
-    if ((rc = dev_copy(ctx, &dob, b_off, (size_t)mb + 2))) return rc;
-    if ((rc = dev_copy(ctx, &dia, ia, (size_t)n))) return rc;
-    if ((rc = dev_copy(ctx, &dib, ib, (size_t)n))) return rc;
+    DevBufs bufs;
+    if ((rc = dev_copy(ctx, bufs, &da, (const uint8_t *)a, (size_t)a_off[ma + 1]))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &db, (const uint8_t *)b, (size_t)b_off[mb + 1]))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &doa, a_off, (size_t)ma + 2))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &dob, b_off, (size_t)mb + 2))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &dia, ia, (size_t)n))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &dib, ib, (size_t)n))) return rc;
     VSK_CUDA(ctx, cudaMalloc(&dout, sizeof(int32_t) * (size_t)n));
+    bufs.v.push_back(dout);
     rc = vsk_lcs_launch(ctx, da, doa, db, dob, dia, dib, n, dout);
     if (rc == VSK_OK) {
         cudaError_t e = cudaMemcpyAsync(out, dout, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) rc = vsk_fail(ctx, VSK_ERR_CUDA, "lcs: %s", cudaGetErrorString(e));
     }
-    cudaFree(da); cudaFree(db); cudaFree(doa); cudaFree(dob); cudaFree(dia); cudaFree(dib); cudaFree(dout);
     return rc;
 }
 
@@ -405,20 +424,21 @@ extern "C" int vsk_ed_pairs(vsk_ctx *ctx, const char *text, const int64_t *t_off
     int64_t *dto = nullptr, *dpo = nullptr;
     int32_t *dtl = nullptr, *dpl = nullptr, *dout = nullptr;
     int rc;
-    if ((rc = dev_copy(ctx, &dt, (const uint8_t *)text, (size_t)tmax))) return rc;
-    if ((rc = dev_copy(ctx, &dp, (const uint8_t *)pat, (size_t)pmax))) return rc;
-    if ((rc = dev_copy(ctx, &dto, t_off, (size_t)n))) return rc;
-    if ((rc = dev_copy(ctx, &dpo, p_off, (size_t)n))) return rc;
-    if ((rc = dev_copy(ctx, &dtl, t_len, (size_t)n))) return rc;
-    if ((rc = dev_copy(ctx, &dpl, p_len, (size_t)n))) return rc;
+    DevBufs bufs;
+    if ((rc = dev_copy(ctx, bufs, &dt, (const uint8_t *)text, (size_t)tmax))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &dp, (const uint8_t *)pat, (size_t)pmax))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &dto, t_off, (size_t)n))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &dpo, p_off, (size_t)n))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &dtl, t_len, (size_t)n))) return rc;
+    if ((rc = dev_copy(ctx, bufs, &dpl, p_len, (size_t)n))) return rc;
     VSK_CUDA(ctx, cudaMalloc(&dout, sizeof(int32_t) * (size_t)n));
+    bufs.v.push_back(dout);
     rc = vsk_ed_launch(ctx, dt, dto, dtl, dp, dpo, dpl, n, variant, dout);
     if (rc == VSK_OK) {
         cudaError_t e = cudaMemcpyAsync(out, dout, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) rc = vsk_fail(ctx, VSK_ERR_CUDA, "ed: %s", cudaGetErrorString(e));
     }
-    cudaFree(dt); cudaFree(dp); cudaFree(dto); cudaFree(dpo); cudaFree(dtl); cudaFree(dpl); cudaFree(dout);
     return rc;
 }
 
@@ -493,8 +513,9 @@ extern "C" int vsk_profile_read(vsk_ctx *ctx, double *dp_ms, int64_t *dp_launche
     double tot = 0;
     for (size_t i = 0; i + 1 < ctx->prof_events.size(); i += 2) {
         float ms = 0;
-        VSK_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->prof_events[i], ctx->prof_events[i + 1]));
-        tot += ms;
+        // a launch that failed half-way leaves its second event unrecorded: skipped
+        if (cudaEventElapsedTime(&ms, ctx->prof_events[i], ctx->prof_events[i + 1]) == cudaSuccess) tot += ms;
+        else cudaGetLastError();
         cudaEventDestroy(ctx->prof_events[i]);
         cudaEventDestroy(ctx->prof_events[i + 1]);
     }

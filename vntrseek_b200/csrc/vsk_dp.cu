@@ -783,9 +783,15 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
     if (K == 0 && (!use_tinydir || !(use_dir && use_dir_q8))) n_tiny = n_q8 = 0;
     const int64_t n_warp = n_jobs - n_tiny - n_q8;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (ctx->profile) {
+    if (ctx->profile) {  // owned by the context from here on (a failure below does not leak them)
         VSK_CUDA(ctx, cudaEventCreate(&e0));
-        VSK_CUDA(ctx, cudaEventCreate(&e1));
+        ctx->prof_events.push_back(e0);
+        if (cudaEventCreate(&e1) != cudaSuccess) {
+            ctx->prof_events.pop_back();
+            cudaEventDestroy(e0);
+            return vsk_fail(ctx, VSK_ERR_CUDA, "cudaEventCreate failed");
+        }
+        ctx->prof_events.push_back(e1);
         VSK_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
     }
     const bool dir_q8 = use_dir && use_dir_q8 && n_q8 > 0;  // the 8-lane jobs take the direction-bit path too
@@ -929,8 +935,6 @@ int vsk_dp_launch(vsk_ctx *ctx, const uint16_t *d_left_ids, const uint16_t *d_to
     }
     if (ctx->profile) {
         VSK_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
-        ctx->prof_events.push_back(e0);
-        ctx->prof_events.push_back(e1);
     }
     vsk_host_acc(ctx, "dp_launch_total", vsk_now_ms() - h0);
     return VSK_OK;

@@ -46,24 +46,53 @@ struct DdWarpSmem {
 };
 #define DD_SMEM_BYTES (2048 + DD_WARPS * sizeof(DdWarpSmem))
 
-// Columns per lane and number of column strips of a pair: the cheapest of 8, 12, 16 columns per lane, in
-// issued instructions per wavefront step (11 per cell + about 50 that do not depend on the strip width).
-// `force` (tuning aid, VSK_DD_FORCE=8|12|16) overrides the choice.
-__host__ __device__ inline void dd_plan(int l2, int force, int &cpl, int &ns) {
+// Column strips of a pair: nm strips of 32*cm columns (cm columns per lane), then -- if cl != 0 -- one last strip
+// of 32*cl columns.  The cheapest arrangement in issued instructions per wavefront step (9 per cell + about 41
+// that do not depend on the strip width): either equal strips of 8, 12 or 16 columns per lane, or strips of 16
+// (or 12) with a narrower or wider last one, which cuts the padding of the last strip (about 5 % of the sweep
+// on the bench's job mix).  `force` (tuning aid, VSK_DD_FORCE): 8|12|16 = equal strips of that width, 1 = equal
+// strips only (the width still chosen per pair), 0 = free choice.
+struct DdPlan {
+    int cm, nm, cl;
+};
+#define DD_CELL_COST 9
+#define DD_STEP_COST 41
+__host__ __device__ inline DdPlan dd_plan(int l2, int force) {
+    DdPlan p = {16, 1, 0};
     int best = 0x7fffffff;
-    cpl = 16;
-    ns = 1;
 #pragma unroll
     for (int c = 16; c >= 8; c -= 4) {
         const int n = (l2 + 32 * c - 1) / (32 * c);
-        const int cost = n * (c * 11 + 50);  // x (l1 + 31) steps either way
-        if (force ? (c == force) : (cost < best)) {
+        const int cost = n * (c * DD_CELL_COST + DD_STEP_COST);  // x (l1 + 31) steps either way
+        if (force > 1 ? (c == force) : (cost < best)) {
             best = cost;
-            cpl = c;
-            ns = n;
+            p.cm = c;
+            p.nm = n;
+            p.cl = 0;
         }
     }
+    if (force == 0) {
+        for (int cm = 16; cm >= 12; cm -= 4) {
+            const int w = 32 * cm;
+            for (int k = 1; k * w < l2; ++k) {
+                const int rem = l2 - k * w;
+                for (int cl = 8; cl <= 16; cl += 4) {
+                    if (32 * cl < rem) continue;
+                    const int cost = k * (cm * DD_CELL_COST + DD_STEP_COST) + cl * DD_CELL_COST + DD_STEP_COST;
+                    if (cl != cm && cost < best) {
+                        best = cost;
+                        p.cm = cm;
+                        p.nm = k;
+                        p.cl = cl;
+                    }
+                    break;  // the narrowest last strip that fits
+                }
+            }
+        }
+    }
+    return p;
 }
+__host__ __device__ inline int dd_strips(const DdPlan &p) { return p.nm + (p.cl ? 1 : 0); }
 
 // row record: bits 0..15 table row offset (local index * nb, or the id for the global table),
 // 16..23 gap cost d(0,l)
@@ -179,22 +208,23 @@ __device__ __forceinline__ void dd_flush8(const DdWarpSmem &ws, int lane, uint32
     __stcs(dst + 1, b);
 }
 
+// One strip of a pair: the 32*CPL columns from column col0 on (strip number `strip` of the pair; first / last:
+// the pair's first / last strip).  totd (gap costs of the columns so far) and prev_r_hi (rows the previous strip
+// left in the boundary scratch) pass from strip to strip.
 template <int CPL, bool SMEMT>
 __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *__restrict__ Tp,
                                         const uint8_t *__restrict__ dist, const uint16_t *s_gapnd, DdWarpSmem &ws,
                                         int nb, int *bscr, const uint32_t *rowrec, uint32_t *__restrict__ dir,
-                                        int4 *out) {
+                                        int4 *out, const int col0, const int strip, const bool first,
+                                        const bool last, int &totd, int &prev_r_hi) {
     const int lane = threadIdx.x & 31;
     const int l1 = job.l1, l2 = job.l2, br = job.br;
     const bool banded = br >= 0;
     const double sv = job.svector;
-    const int npass = (l2 + (32 * CPL) - 1) / (32 * CPL);
-    int totd = 0;
     int Hd[CPL];
-    int prev_r_hi = l1;
 
-    for (int pass = 0; pass < npass; ++pass) {
-        const int cbase = pass * (32 * CPL) + lane * CPL;
+    {
+        const int cbase = col0 + lane * CPL;
         int tb[CPL], gt[CPL];
         int sd = 0;
 #pragma unroll
@@ -231,7 +261,7 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
         // rows whose band can touch this strip (conservative; the per-cell mask stays exact)
         int r_lo = 0, r_hi = l1;
         if (banded) {
-            const int c0 = pass * (32 * CPL);
+            const int c0 = col0;
             const double a = (double)(c0 + 1 - br), b = (double)(min(l2, c0 + (32 * CPL)) + br + 1);
             r_lo = max(0, (int)floor(a / sv) - 2);
             r_hi = min(l1, (int)ceil(b / sv) + 2);
@@ -242,13 +272,12 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
             for (int j = 0; j < CPL; ++j) Hd[j] = VSK_BIG;
             dgd = VSK_BIG;
         }
-        const bool first = (pass == 0);
-        const bool wr_scratch = (lane == 31) && (pass < npass - 1);
+        const bool wr_scratch = (lane == 31) && !last;
         int nxt = VSK_BIG;
         if (lane == 0 && !first && r_lo < prev_r_hi) nxt = __ldcg(bscr + r_lo);
         uint32_t rec_next = __ldcg(rowrec + min(max(r_lo - lane, 0), l1 - 1));
         const int l1p = (l1 + 7) & ~7;
-        uint32_t *dlane = dir + (size_t)(pass * 32 + lane) * l1p;  // this lane's words, row-indexed
+        uint32_t *dlane = dir + (size_t)(strip * 32 + lane) * l1p;  // this lane's words, row-indexed
         const int g_lo = r_lo & ~7;
 
         // a step with range checks: pipeline fill and drain (lanes whose row is outside [r_lo, r_hi) idle)
@@ -355,12 +384,14 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
         prev_r_hi = r_hi;
         __syncwarp();
     }
-    const int cl = (l2 - 1) - (npass - 1) * (32 * CPL);
-    if (lane == cl / CPL) {
-        const int jr = cl % CPL;
+    if (last) {
+        const int cl = (l2 - 1) - col0;
+        if (lane == cl / CPL) {
+            const int jr = cl % CPL;
 #pragma unroll
-        for (int j = 0; j < CPL; ++j)
-            if (j == jr) out[job.out_idx] = make_int4(Hd[j], 0, 0, 0);
+            for (int j = 0; j < CPL; ++j)
+                if (j == jr) out[job.out_idx] = make_int4(Hd[j], 0, 0, 0);
+        }
     }
 }
 
@@ -393,18 +424,34 @@ vsk_dp_dir_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__restr
         int nb = 0;
         const bool smemt = dd_setup(L, Tp, job.l1, job.l2, dist, s_gapnd, ws, my_rowrec, nb);
         uint32_t *dir = dirbuf + (dir_off[ji] - (int64_t)batch * batch_words);
-        int cpl, ns;
-        dd_plan(job.l2, force, cpl, ns);
-#define DD_DISPATCH(C)                                                                       \
-    do {                                                                                     \
-        if (smemt) dd_pair<C, true>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out); \
-        else dd_pair<C, false>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out);      \
+        int totd = 0, prev_r_hi = job.l1;
+        // strip by strip; ONE dispatch inside the loop, so that every instantiation of dd_pair exists once in
+        // the kernel (code size).  The plan is recomputed per strip instead of being kept in
+        // registers across the sweep (the kernel runs at its register limit).
+        int ns = 1;
+#pragma unroll 1
+        for (int strip = 0; strip < ns; ++strip) {
+            const DdPlan plan = dd_plan(job.l2, force);
+            ns = dd_strips(plan);
+            const bool tail = strip >= plan.nm;  // the last strip of a mixed plan
+            const int cpl = tail ? plan.cl : plan.cm;
+            const int col0 = tail ? plan.nm * 32 * plan.cm : strip * 32 * plan.cm;
+            const bool sf = (strip == 0), sl = (strip == ns - 1);
+#define DD_DISPATCH(C)                                                                                              \
+    do {                                                                                                            \
+        if (smemt)                                                                                                  \
+            dd_pair<C, true>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out, col0, strip, sf, sl, totd, \
+                             prev_r_hi);                                                                            \
+        else                                                                                                        \
+            dd_pair<C, false>(job, Tp, dist, s_gapnd, ws, nb, my_bscr, my_rowrec, dir, out, col0, strip, sf, sl,     \
+                              totd, prev_r_hi);                                                                     \
     } while (0)
-        if (cpl == 16) DD_DISPATCH(16);
-        else if (cpl == 12) DD_DISPATCH(12);
-        else DD_DISPATCH(8);
+            if (cpl == 16) DD_DISPATCH(16);
+            else if (cpl == 12) DD_DISPATCH(12);
+            else DD_DISPATCH(8);
 #undef DD_DISPATCH
-        __syncwarp();
+            __syncwarp();
+        }
     }
 }
 
@@ -586,13 +633,34 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
         const uint16_t *Tp = top_ids + job.top_off;
         const uint32_t *dir = dirbuf + (off0 - (int64_t)batch * batch_words);
         const int l1p = (job.l1 + 7) & ~7;
-        int cpl, ns;
-        if (ji >= q_begin) cpl = dq_cpl(job.l2);  // 8-lane job
-        else dd_plan(job.l2, force, cpl, ns);
+        // columns [0, main_cols) sit in lanes of cm columns, the rest (the last strip of a mixed plan) in lanes of
+        // cl columns that start at lane index main_lanes
+        int cm, cl = 0, main_cols = 0x7fffffff, main_lanes = 0x7fffffff;
+        if (ji >= q_begin) {
+            cm = dq_cpl(job.l2);  // 8-lane job
+        } else {
+            const DdPlan plan = dd_plan(job.l2, force);
+            cm = plan.cm;
+            if (plan.cl) {
+                cl = plan.cl;
+                main_lanes = plan.nm * 32;
+                main_cols = main_lanes * cm;
+            }
+        }
         int r = job.l1, c = job.l2;
         int p1 = 0, sumw = 0, len = 0;
         // position of column c-1 inside the strips: strip*32 + lane, cell
-        int sl = (c - 1) / cpl, j = (c - 1) - sl * cpl;
+        int cpl, sl, j;
+        if (c - 1 < main_cols) {
+            cpl = cm;
+            sl = (c - 1) / cm;
+            j = (c - 1) - sl * cm;
+        } else {
+            cpl = cl;
+            sl = (c - 1 - main_cols) / cl;
+            j = (c - 1 - main_cols) - sl * cl;
+            sl += main_lanes;
+        }
         uint32_t w = 0;
         int wr = -1, wl = -1;  // (row, strip*32+lane) of the cached word
         const bool banded = job.br >= 0;
@@ -618,7 +686,8 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
                     // into L2 while this one is in flight
                     const int pr = r - 1 - DT_AHEAD;
                     if (pr >= 0) {
-                        const int pc = max(c - 1 - DT_AHEAD, 0) / cpl;
+                        const int pcol = max(c - 1 - DT_AHEAD, 0);
+                        const int pc = pcol < main_cols ? pcol / cm : main_lanes + (pcol - main_cols) / cl;
                         asm volatile("prefetch.global.L2 [%0];" ::"l"(dir + (size_t)pc * l1p + pr));
                     }
                 }
@@ -649,8 +718,9 @@ vsk_dp_trace_kernel(const uint16_t *__restrict__ left_ids, const uint16_t *__res
             if (left) {
                 --c;
                 if (--j < 0) {
-                    j = cpl - 1;
                     --sl;
+                    if (sl < main_lanes) cpl = cm;  // out of the last strip of a mixed plan
+                    j = cpl - 1;
                 }
             }
             ++len;
@@ -684,9 +754,7 @@ __global__ void vsk_dd_words_kernel(const vsk_dp_job *__restrict__ jobs, int n, 
         words[i] = DQ_G * l1p;
         return;
     }
-    int cpl, ns;
-    dd_plan(l2, force, cpl, ns);
-    words[i] = VSK_DP_DIRJOB(l2) ? (int64_t)ns * 32 * l1p : 0;
+    words[i] = VSK_DP_DIRJOB(l2) ? (int64_t)dd_strips(dd_plan(l2, force)) * 32 * l1p : 0;
 }
 
 // bounds[b] = first job whose direction words start at or after b*batch_words (jobs of a batch are
@@ -725,11 +793,11 @@ static int dd_reserve(vsk_ctx *ctx, int k, size_t bytes, void **out) {
     return VSK_OK;
 }
 
-static int dd_force() {  // tuning aid: VSK_DD_FORCE=8|12|16 fixes the columns per lane of the sweep
+static int dd_force() {  // tuning aid: VSK_DD_FORCE=8|12|16 fixes the columns per lane of the sweep, 1 = equal strips only
     static const int force = [] {
         const char *e = getenv("VSK_DD_FORCE");
         const int c = e ? atoi(e) : 0;
-        return (c == 8 || c == 12 || c == 16) ? c : 0;
+        return (c == 8 || c == 12 || c == 16 || c == 1) ? c : 0;
     }();
     return force;
 }
