@@ -156,6 +156,12 @@ int vsk_pair_dp_static(vsk_ctx *ctx, const uint16_t *d_left_ids, int64_t n_left_
                        int64_t n, vsk_dp_result *d_out);
 /* band geometry of GetFixedProfileAPNarrowband (profile.h:1752-1770), host libm */
 int vsk_band_params(int32_t l1, int32_t l2, int homology, double *svector, int32_t *br);
+/* Diagnostic (no GPU needed): how the forward sweep of the profile DP (the library's replacement of
+ * GetFixedProfileAP's row loop, profile.h:2092-2128) cuts the l2 columns of a pair into strips:
+ * plan[0] columns per lane in each of plan[1] strips of 32 lanes, then -- if plan[2] != 0 -- one last
+ * strip of plan[2] columns per lane.  force: 0 = the library's choice, 1 = equal strips only,
+ * 8|12|16 = equal strips of that width (the values of VSK_DD_FORCE).                               */
+int vsk_dd_plan(int32_t l2, int force, int32_t plan[3]);
 
 /* ---- string sets (consensus sequences, flanks) -----------------------------
  * ASCII, concatenated; off[n+1] byte offsets.                                */

@@ -793,6 +793,15 @@ static int dd_reserve(vsk_ctx *ctx, int k, size_t bytes, void **out) {
     return VSK_OK;
 }
 
+extern "C" int vsk_dd_plan(int32_t l2, int force, int32_t plan[3]) {
+    if (!plan || l2 < 1 || !(force == 0 || force == 1 || force == 8 || force == 12 || force == 16)) return VSK_ERR_ARG;
+    const DdPlan p = dd_plan(l2, force);
+    plan[0] = p.cm;
+    plan[1] = p.nm;
+    plan[2] = p.cl;
+    return VSK_OK;
+}
+
 static int dd_force() {  // tuning aid: VSK_DD_FORCE=8|12|16 fixes the columns per lane of the sweep, 1 = equal strips only
     static const int force = [] {
         const char *e = getenv("VSK_DD_FORCE");
