@@ -308,18 +308,19 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                 if (g0 >= g_lo) dd_flush8(ws, lane, dlane, g0);
             }
         };
-        // Steps r_lo .. r_hi+30.  The middle ones, where every lane has a row, run in the steady loop below,
-        // two rows per trip (so their number is made even: an odd one out is taken by the checked step).
+        // Steps r_lo .. r_hi+30.  The middle ones, where every lane has a row, run in the steady loop below in
+        // blocks of 8 steps (two rows per trip, four trips, then the flush of the block's direction words); the
+        // steady phase starts on a multiple of 8 steps, so that the flush and the window refill need no test
+        // per step.  What is left over on either side goes through the checked step.
         const int s_fill_end = min(r_lo + 31, r_hi + 31);
-        const int n_steady = max(0, r_hi - s_fill_end);
-        const int s_steady_begin = s_fill_end + (n_steady & 1);
+        const int s_steady_begin = min((s_fill_end + 7) & ~7, r_hi + 31);
         int s = r_lo;
 #pragma unroll 1
         for (int phase = 0; phase < 2; ++phase) {  // one copy of the checked step serves fill and drain
             const int lim = phase ? r_hi + 31 : s_steady_begin;
 #pragma unroll 1
             for (; s < lim; ++s) step(s);
-            if (phase == 0 && s < r_hi) {
+            if (phase == 0 && s + 8 <= r_hi) {
                 // steady phase: every lane has a row in [r_lo, r_hi) and every step sends a row out; the
                 // addresses advance by one row per step (the scratch has a row of slack past l1)
                 int *bp = bscr + (s - lane);                   // lane 31 leaves its row's last cell here
@@ -338,10 +339,6 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                 // runs it twice per trip with the two arrays swapping roles, so no row is copied.
                 auto steady = [&](const int (&Hin)[CPL], int (&Hout)[CPL]) {
                     const int r = s - lane;
-                    if ((k & 31) == 0) {  // rows s+33 .. s+64: needed from step s+32 on
-                        wpre = __ldcg(rowrec + s + 33 + lane);
-                        if (!first) bpre = __ldcg(bscr + s + 33 + lane);
-                    }
                     int lfd = __shfl_up_sync(DD_FULL, Hin[CPL - 1], 1);
                     const uint32_t rec = rec_next;
                     rec_next = ws.win[(r + 1) & 63];
@@ -355,24 +352,31 @@ __device__ __forceinline__ void dd_pair(const vsk_dp_job &job, const uint16_t *_
                     ws.u.ring[lane][r & 15] = w;
                     if (wr_scratch) *bp = Hout[CPL - 1];
                     ++bp;
-                    if ((s & 7) == 7) {  // the lane's last complete group of 8 rows goes out
-                        const int g0 = ((r + 1) & ~7) - 8;
-                        if (g0 >= g_lo) dd_flush8(ws, lane, dlane, g0);
-                    }
-                    if ((k & 31) == 31) {  // rows <= s-31 are done with: their slots take rows s+2 .. s+33
-                        __syncwarp();
-                        ws.win[(s + 2 + lane) & 63] = wpre;
-                        bcur = bpre;
-                        __syncwarp();
-                    }
                     ++s;
                     ++k;
                 };
                 int Hx[CPL];
 #pragma unroll 1
-                while (s < r_hi) {
-                    steady(Hd, Hx);
-                    steady(Hx, Hd);
+                while (s + 8 <= r_hi) {
+                    if ((k & 31) == 0) {  // rows s+33 .. s+64: needed from step s+32 on
+                        wpre = __ldcg(rowrec + s + 33 + lane);
+                        if (!first) bpre = __ldcg(bscr + s + 33 + lane);
+                    }
+#pragma unroll 1
+                    for (int q = 0; q < 4; ++q) {
+                        steady(Hd, Hx);
+                        steady(Hx, Hd);
+                    }
+                    {  // s is a multiple of 8 again: the lane's last complete group of 8 rows goes out
+                        const int g0 = ((s - lane) & ~7) - 8;
+                        if (g0 >= g_lo) dd_flush8(ws, lane, dlane, g0);
+                    }
+                    if ((k & 31) == 0) {  // rows <= s-32 are done with: their slots take rows s+1 .. s+32
+                        __syncwarp();
+                        ws.win[(s + 1 + lane) & 63] = wpre;
+                        bcur = bpre;
+                        __syncwarp();
+                    }
                 }
             }
         }
