@@ -537,6 +537,41 @@ __device__ __forceinline__ void dq_pair(const vsk_dp_job &job, const uint16_t *_
     const int s_fill_end = min(DQ_G - 1, l1 + DQ_G - 1);
     int s = 0;
     for (; s < s_fill_end; ++s) step(s, true);
+    {  // steady phase (every lane of the group has a row): blocks of 8 steps from a multiple of 8 on, two rows per
+       // trip with the two register rows swapping roles, the block's direction words flushed after it
+        const int s_al = min((s + 7) & ~7, l1);
+        for (; s < s_al; ++s) step(s, false);
+        auto lean = [&](const int (&Hin)[CPL], int (&Hout)[CPL]) {
+            const int r = s - glane;
+            int lfd = __shfl_up_sync(gmask, Hin[CPL - 1], 1, DQ_G);
+            const int id = id_next;
+            id_next = L[min(r + 1, l1 - 1)];
+            const int gl = s_gapnd[id] & 255;
+            const uint8_t *trow = DENSE ? (s_ktab + (int)s_dense[id] * K) : (dist + id * VSK_DROW);
+            if (glane == 0) lfd = dgd + gl;  // column 0, profile.h:2084-2090
+            const uint32_t w = dd_row_cells<CPL, DENSE>(Hin, Hout, tb, gt, dgd, lfd, trow, gl);
+            dgd = lfd;
+            ring[r & 15] = w;
+            ++s;
+        };
+        int Hx[CPL];
+#pragma unroll 1
+        while (s + 8 <= l1) {
+#pragma unroll 1
+            for (int q = 0; q < 4; ++q) {
+                lean(Hd, Hx);
+                lean(Hx, Hd);
+            }
+            const int g0 = ((s - glane) & ~7) - 8;
+            if (g0 >= 0) {
+                const uint4 a = *reinterpret_cast<const uint4 *>(ring + (g0 & 15));
+                const uint4 b = *reinterpret_cast<const uint4 *>(ring + (g0 & 15) + 4);
+                uint4 *dst = reinterpret_cast<uint4 *>(dlane + g0);
+                __stcs(dst, a);
+                __stcs(dst + 1, b);
+            }
+        }
+    }
     for (; s < l1; ++s) step(s, false);
     for (; s < l1 + DQ_G - 1; ++s) step(s, true);
     {  // the rows after the last complete group (and that group once more)
