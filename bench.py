@@ -42,7 +42,7 @@ import numpy as np  # noqa: E402
 
 # bytes: dram read+write of one vsk_dp_dir_kernel launch at the default workload (ncu --set full,
 # profiles/): refreshed whenever the kernel or the batch size changes
-DIR_TRAFFIC = {"bytes": 11.73e9, "source": "profiles/r02_summary.md section D (launch 0: a 12 GiB batch of the first chunk)"}
+DIR_TRAFFIC = {"bytes": 11.74e9, "source": "profiles/r02_summary.md section F (launch 0: a 12 GiB batch of the first chunk)"}
 METRIC = "proclu_read_TRs_mapped_per_sec"
 UNIT = "read-TRs/s"
 OPS_PER_CELL = 14        # algorithmic integer operations per profile-DP cell
@@ -587,7 +587,7 @@ def ours(args, rank, world, local_rank):
                 "dp_stage": {"ms_per_step": dp_ms / K, "gcups": stage_gcups,
                              "achieved": OPS_PER_CELL * stage_gcups,
                              "frac": OPS_PER_CELL * stage_gcups / int_peak if int_peak else None,
-                             "kernels": "vsk_dp_dir_kernel + vsk_dp_q8dir_kernel + vsk_dp_tiny_kernel + "
+                             "kernels": "vsk_dp_dir_kernel + vsk_dp_q8dir_kernel + vsk_dp_tinydir_kernel + "
                                         "vsk_dp_trace_kernel (+ vsk_dp_kernel for handed-back pairs), two side streams"},
             },
         }
