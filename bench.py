@@ -118,7 +118,13 @@ class ClockSampler:
             self.p = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                        "-lms", str(int(period_ms))],
                                       stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.first = self.p.stdout.readline()  # attached: the first sample is out
+            import select
+            ready, _, _ = select.select([self.p.stdout], [], [], 60.0)
+            if ready:
+                self.first = self.p.stdout.readline()  # attached: the first sample is out
+            else:  # never produced a line: do without it rather than hang the bench
+                self.p.kill()
+                self.p = None
         except OSError:
             self.p = None
 
