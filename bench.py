@@ -553,12 +553,13 @@ def ours(args, rank, world, local_rank):
             "dp_cells_per_step": cells,
             "counters_rank0": {k: stats[k] for k in ("candidates_considered", "lcs_alignments", "profile_alignments",
                                                       "profile_alignments_success", "confirmed", "chunks")},
-            "stage_ms_per_step": {k: val / K for k, val in stages.items()},
+            "stage_ms_per_step": {k: val / K for k, val in stages.items() if not k.startswith("host_")},
+            "host_ms_per_step": {k[5:]: val / K for k, val in stages.items() if k.startswith("host_")},
             "index_build_s": index_s, "datagen_s": gen_s, "pack_s": pack_s,
             "e2e": {"value": total_reads / (e2e_step_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": st2["h2d_bytes"], "d2h_bytes_per_step": d2h_links,
                     "ms_per_step": e2e_step_ms,
-                    "stage_ms_per_step": {k: val / K for k, val in e2e_stages.items()}},
+                    "stage_ms_per_step": {k: val / K for k, val in e2e_stages.items() if not k.startswith("host_")}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {
