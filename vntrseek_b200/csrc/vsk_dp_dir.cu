@@ -12,9 +12,10 @@
 // lane own 16 columns (strips of 512) at fewer registers, i.e. fewer instructions per cell and less
 // per-step overhead.  The trace costs L1+L2 dependent steps per pair, run one pair per thread.
 //
-// Direction words: one uint32 per (row, lane) of a strip = the CPL (8, 12 or 16, chosen per pair by
-// dd_plan so that the strips fit the pair) cells of that lane; cell j holds "not diagonal" in bit
-// 2(CPL-1-j)+1 and "right rather than down" in bit 2(CPL-1-j).  They are stored lane-major: the words
+// Direction words: one uint32 per (row, lane) of a strip = the CPL (8, 12 or 16 per strip, arranged per pair by
+// dd_plan so that the strips fit the pair) cells of that lane; cell j holds "right" in bit 2(CPL-1-j) and,
+// looked at only when that bit is clear, "down rather than diagonal" in bit 2(CPL-1-j)+1 (dd_row_cells).
+// They are stored lane-major: the words
 // of one lane (strip*32 + lane) for rows 0..l1-1 are contiguous (padded to 8 rows), because that is
 // how the trace reads them -- a path stays in one lane's columns for about CPL rows, so eight of its
 // steps share a 32-byte sector.  A lane parks its words in a 16-row ring in shared memory and every
